@@ -56,6 +56,21 @@ struct FixedSampler : public PathSampleGenerator {
     UniformSampler &uniformGenerator() override { return uni; }
 };
 
+// H-uninit: with "useAnisoMtx": false the reference only ever writes the DIAGONALS of the
+// default-constructed Eigen matrices _local_to_world / _world_to_local (GPFunctions.cpp:661-667); the off-diagonals
+// are whatever the heap held.  On a fresh heap that is zero, which is what every reference render relies on;
+// in a long-lived test process it is not (observed here: NaN gradients on the 3rd medium created).  The harness
+// therefore pins the intended state: off-diagonals zero, transposes recomputed.  No arithmetic is restated.
+void pinDiagonalTransforms(StationaryCovariance *cov) {
+    auto *se = dynamic_cast<SquaredExponentialCovariance *>(cov);
+    if (!se || se->_use_aniso_mtx) return;
+    for (int i = 0; i < 3; ++i)
+        for (int j = 0; j < 3; ++j)
+            if (i != j) { se->_local_to_world(i, j) = 0.f; se->_world_to_local(i, j) = 0.f; }
+    se->_local_to_world_transpose = se->_local_to_world.transpose();
+    se->_world_to_local_transpose = se->_world_to_local.transpose();
+}
+
 SparseConvolutionNoiseRealization makeRealization(const RefMedium *m) {
     auto *s = m->scn;
     auto gp = s->_gp->get_gaussian_process();
@@ -123,6 +138,11 @@ void *ref_medium_create(const char *medium_json) {
         m->medium->prepareForRender();
         m->scn = dynamic_cast<SparseConvolutionNoiseMedium *>(m->medium.get());
         if (!m->scn) { g_err = "medium is not of type sparse_conv_noise"; return nullptr; }
+        {
+            auto gp = m->scn->_gp->get_gaussian_process();
+            if (auto *st = dynamic_cast<StationaryCovariance *>(gp->_cov.get())) pinDiagonalTransforms(st);
+            else if (auto *ns = dynamic_cast<NonstationaryCovariance *>(gp->_cov.get())) pinDiagonalTransforms(ns->_stationaryCov.get());
+        }
         return m.release();
     } catch (const std::exception &e) {
         g_err = e.what();

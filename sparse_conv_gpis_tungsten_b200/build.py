@@ -1,0 +1,62 @@
+"""In-tree build of the CUDA library (sm_100a only) and, as a separate artefact, of the test oracle.
+
+`build_library()` compiles csrc/*.cu + csrc/*.cpp into libscn_b200.so next to this file with
+    nvcc -gencode arch=compute_100a,code=sm_100a -lineinfo
+(nvcc cross-compiles without a GPU).  The CUDA runtime is linked statically, so the .so travels to the GPU box.
+`build_oracle()` runs oracle/Makefile (`oracle` always; `ref` only where /root/reference exists) — building the
+checker is not using it: nothing in this package imports or loads anything under oracle/.
+"""
+import os
+import shutil
+import subprocess
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(HERE)
+CSRC = os.path.join(HERE, "csrc")
+LIB = os.path.join(HERE, "libscn_b200.so")
+SOURCES = ["scn_api.cu", "scn_json.cpp"]
+HEADERS = ["scn_device.cuh", "scn_fast.cuh", "scn_march.cuh", "scn_internal.h", os.path.join("..", "..", "include", "scn.h")]
+NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "-Xcompiler", "-fPIC,-O2", "-shared"]
+
+
+def _nvcc():
+    for cand in (shutil.which("nvcc"), "/usr/local/cuda/bin/nvcc"):
+        if cand and os.path.exists(cand):
+            return cand
+    raise RuntimeError("nvcc not found: the library has no CPU build")
+
+
+def _stale(target, deps):
+    if not os.path.exists(target):
+        return True
+    t = os.path.getmtime(target)
+    return any(os.path.exists(d) and os.path.getmtime(d) > t for d in deps)
+
+
+def build_library(force=False, verbose=False):
+    srcs = [os.path.join(CSRC, s) for s in SOURCES]
+    deps = srcs + [os.path.join(CSRC, h) for h in HEADERS]
+    if not force and not _stale(LIB, deps):
+        return LIB
+    cmd = [_nvcc()] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-o", LIB] + srcs
+    res = subprocess.run(cmd, capture_output=True, text=True)
+    if res.returncode != 0:
+        raise RuntimeError("nvcc failed:\n" + " ".join(cmd) + "\n" + res.stdout + res.stderr)
+    if verbose:
+        print(res.stderr)
+    return LIB
+
+
+def build_oracle(with_reference=None):
+    """Compile oracle/scn_oracle.c (always) and oracle/_ref (only when the reference tree is mounted)."""
+    odir = os.path.join(ROOT, "oracle")
+    subprocess.run(["make", "-s", "-C", odir, "oracle"], check=True)
+    if with_reference is None:
+        with_reference = os.path.isdir("/root/reference/src/core")
+    if with_reference:
+        subprocess.run(["make", "-s", "-j", str(os.cpu_count() or 1), "-C", odir, "ref"], check=True)
+    return os.path.join(odir, "_build", "libscn_oracle.so")
+
+
+if __name__ == "__main__":
+    print(build_library(force=True, verbose=True))

@@ -1,0 +1,541 @@
+// scn_api.cu — C ABI (include/scn.h) + kernels of the B200-native sparse-convolution-noise GPIS medium.
+//
+// One thread marches one ray / evaluates one point; per-ray Renewal state (Coeff: 7 floats) stays in registers for
+// the whole query.  There is no CPU fallback: without a CUDA device every compute entry point returns SCN_ECUDA.
+#include <cuda_runtime.h>
+
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <new>
+
+#include "scn_device.cuh"
+#include "scn_fast.cuh"
+
+namespace scn {
+
+static thread_local char g_err[512] = "";
+int set_error(int code, const char *fmt, ...) {
+    va_list ap; va_start(ap, fmt); vsnprintf(g_err, sizeof g_err, fmt, ap); va_end(ap);
+    return code;
+}
+static int cuda_fail(cudaError_t e, const char *what) { return set_error(SCN_ECUDA, "%s: %s", what, cudaGetErrorString(e)); }
+#define SCN_CUDA(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) return cuda_fail(e_, #x); } while (0)
+
+// ---------------------------------------------------------------- host: descriptor -> kernel parameters
+static float host_se_variance3d(const Params &p, float R, bool is_identity, float gs, float ls) { // GPF:741-754
+    double per_unit = p.density / (R * R * R);
+    double det_sqrt = 1.0;
+    if (!is_identity) { det_sqrt = p.l_aniso[0] * p.l_aniso[1] * p.l_aniso[2]; det_sqrt *= std::pow((double)gs, 3); }
+    det_sqrt *= std::pow((double)ls, 3);
+    double integral = std::pow(M_PI, 1.5) * det_sqrt;
+    return (float)(per_unit * integral);
+}
+static void field_k(const scn_field_desc &f, FieldK &k) {
+    memset(&k, 0, sizeof k);
+    k.type = f.type;
+    for (int i = 0; i < 3; ++i) k.val[i] = f.val[i];
+    const double c = 1.; // _const (never read from JSON)
+    double mn = f.min + c, mx = f.max + c, mn2 = f.min2 + c, mx2 = f.max2 + c;
+    k.la[0] = std::log(mn * mn); k.lb[0] = std::log(mx * mx); k.scale[0] = 1.0 / (f.end - f.start); k.off[0] = -f.start * k.scale[0];
+    k.la[1] = std::log(mn2 * mn2); k.lb[1] = std::log(mx2 * mx2); k.scale[1] = 1.0 / (f.end2 - f.start2); k.off[1] = -f.start2 * k.scale[1];
+}
+
+int params_from_desc(const scn_medium_desc &d, Params &p) {
+    memset(&p, 0, sizeof p);
+    if (d.correlation_context < SCN_CTX_GLOBAL || d.correlation_context > SCN_CTX_NONE)
+        return set_error(SCN_EINVAL, "correlation_context is mandatory (media/GaussianProcessMedium.cpp:104-106)");
+    if (d.use_aniso_mtx) return set_error(SCN_EUNSUPPORTED, "useAnisoMtx is not covered");
+    if (d.cov_type != SCN_COV_SQUARED_EXPONENTIAL && d.cov_type != SCN_COV_PROC_NONSTATIONARY) return set_error(SCN_EINVAL, "bad cov_type");
+    if (d.mean.type < SCN_MEAN_HOMOGENEOUS || d.mean.type > SCN_MEAN_LINEAR) return set_error(SCN_EINVAL, "bad mean type");
+    if (!(d.impulse_density >= 0.f) || d.impulse_density > 4096.f) return set_error(SCN_EINVAL, "impulse_density out of range");
+    if (d.min_step == 0) return set_error(SCN_EINVAL, "min_step must be positive");
+    p.n_imp = (uint32_t)d.impulse_density; p.density = d.impulse_density; p.global_seed = d.seed;
+    p.single_realization = d.single_realization; p.iso3d = d.isotropic_3d_sampling; p.sampling_1d = d.sampling_1d;
+    p.ctx = d.correlation_context; p.corr_xy = d.correlation_xy;
+    p.activate_conditioning = !d.single_realization && (d.correlation_context == SCN_CTX_RENEWAL || d.correlation_context == SCN_CTX_RENEWAL_PLUS);
+    p.scheme = (!d.single_realization && d.sampling_1d) ? d.sampling_scheme_1d : SCN_SCHEME_UNI;
+    p.stationary = d.cov_type == SCN_COV_SQUARED_EXPONENTIAL;
+    p.multires = !p.stationary && d.multires;
+    p.surf_vol_sep = d.surf_vol_phase_separate; p.surf_vol_thresh = d.surf_vol_phase_amp_thresh;
+    p.step_size = d.step_size; p.min_step = d.min_step; p.max_bounces = d.max_bounces;
+    { float sa = d.sigma_a * d.density, ss = d.sigma_s * d.density, st = sa + ss; p.absorption_only = ss == 0.0f; p.sigma_s_over_t = ss / st; }
+    p.sigma = d.sigma; p.kernel_scale = d.kernel_scale;
+    float l_conv = d.length_scale * std::sqrt(2.f) / 2; // GPF:658
+    for (int i = 0; i < 3; ++i) {
+        p.l_aniso[i] = l_conv * d.aniso[i];
+        float inv = 1.0f / p.l_aniso[i];
+        p.l_aniso_inv[i] = (std::isinf(inv) || std::isnan(inv)) ? 0.f : inv; // filterWithZero
+    }
+    p.l_aniso_max = std::fmax(std::fmax(p.l_aniso[0], p.l_aniso[1]), p.l_aniso[2]);
+    p.ls_max = 1.f;
+    if (!p.stationary && d.ls.type != SCN_FIELD_NONE) {
+        const scn_field_desc &f = d.ls;
+        if (f.type == SCN_FIELD_CONSTANT) p.ls_max = (float)std::fmax(std::fmax(f.val[0], f.val[1]), f.val[2]);
+        else if (f.type == SCN_FIELD_BOTTOM_TOP_LEFT_RIGHT) p.ls_max = (float)(std::fmax(f.max, f.min) * std::fmax(f.max2, f.min2));
+        else p.ls_max = (float)std::fmax(f.max, f.min);
+    }
+    field_k(d.ls, p.ls); field_k(d.var, p.var);
+    if (p.stationary) { p.ls.type = SCN_FIELD_NONE; p.var.type = SCN_FIELD_NONE; }
+    p.log_base = std::log(2.5f);
+    p.world_scale = p.stationary ? 1.f : p.ls_max;
+    p.add_seed_world = (int)std::floor(std::log(p.world_scale) / std::log(2.5f));
+    p.R_iso = d.kernel_scale;
+    {   // splattingKernelRadius(false, 1.0) (GPF:696-709, 1245-1249)
+        float ls = 1.0f;
+        if (!p.stationary) { ls *= p.multires ? 1.0 : p.ls_max; ls *= 1.f; }
+        p.R_world = d.kernel_scale * ls * p.l_aniso_max;
+    }
+    p.nf_iso = std::sqrt(host_se_variance3d(p, p.R_iso, true, 1.0f, 1.0f));
+    p.nf_world = std::sqrt(host_se_variance3d(p, p.R_world, false, p.world_scale, 1.0f));
+    { double per_unit = p.density / p.R_iso; double integral = std::sqrt(M_PI) * 1.0f; p.nf_1d = std::sqrt((float)(per_unit * integral)); }
+    for (int i = 0; i < LVL_COUNT; ++i) {
+        int k = LVL_MIN + i;
+        float s = std::pow(2.5f, (float)k); // powf, like pow(_base, level) in SCN:64-65
+        p.lvl_scale[i] = s;
+        p.lvl_add_seed[i] = (int)std::floor(std::log(s) / std::log(2.5f));
+        p.lvl_R_world[i] = d.kernel_scale * s * p.l_aniso_max;
+        p.lvl_nf_world[i] = std::sqrt(host_se_variance3d(p, p.lvl_R_world[i], false, s, 1.0f));
+    }
+    p.gp_id = d.gp_id; p.has_mean_add = d.has_mean_additional; p.id_add = d.id_additional;
+    p.mean = d.mean; p.mean_add = d.mean_additional;
+    return SCN_OK;
+}
+
+// ---------------------------------------------------------------- kernels
+constexpr int BLOCK = 128;
+
+struct EvalIn { const float *px, *py, *pz, *dx, *dy, *dz, *t, *info_t; const uint32_t *ix, *iy, *is, *ig; uint32_t scene_seed, noise_seed; const float *ctx[7]; };
+struct EvalOut { float *val, *gx, *gy, *gz; int32_t *gp_id; };
+
+__device__ __forceinline__ Info load_info(const uint32_t *ix, const uint32_t *iy, const uint32_t *is, const uint32_t *ig, uint32_t scene_seed, const float *info_t, size_t i) {
+    Info in; in.px = ix ? ix[i] : 0u; in.py = iy ? iy[i] : 0u; in.spp = is ? is[i] : 0u; in.seg = ig ? ig[i] : 0u; in.scene_seed = scene_seed; in.t = info_t ? info_t[i] : 0.f;
+    return in;
+}
+__device__ __forceinline__ Coeff load_coeff(const float *const ctx[7], size_t i) {
+    Coeff c; c.vs = 0.f; c.gs = F3(0.f, 0.f, 0.f); c.org = F3(0.f, 0.f, 0.f);
+    if (ctx[0]) { c.vs = ctx[0][i]; c.gs = F3(ctx[1][i], ctx[2][i], ctx[3][i]); c.org = F3(ctx[4][i], ctx[5][i], ctx[6][i]); }
+    return c;
+}
+
+// generic noise-level evaluation (any configuration)
+__global__ void __launch_bounds__(BLOCK) k_eval_noise(const __grid_constant__ Params P, const EvalIn in, const EvalOut out, size_t n) {
+    size_t i = (size_t)blockIdx.x * BLOCK + threadIdx.x;
+    if (i >= n) return;
+    f3 p = F3(in.px[i], in.py[i], in.pz[i]), d = F3(in.dx[i], in.dy[i], in.dz[i]);
+    Coeff c; c.vs = 0.f; c.gs = F3(0.f, 0.f, 0.f); c.org = F3(0.f, 0.f, 0.f);
+    Frame fr = ray_frame(P, d);
+    f4 v = P.sampling_1d ? noise1d_norm(P, c, fr, p, in.noise_seed, 1.0f, 0, false, false) : eval_noise3d(P, c, fr, p, in.noise_seed, false);
+    if (out.val) out.val[i] = v.x;
+    if (out.gx) { out.gx[i] = v.y; out.gy[i] = v.z; out.gz[i] = v.w; }
+}
+
+__global__ void __launch_bounds__(BLOCK) k_eval(const __grid_constant__ Params P, const EvalIn in, const EvalOut out, size_t n, int what) {
+    size_t i = (size_t)blockIdx.x * BLOCK + threadIdx.x;
+    if (i >= n) return;
+    f3 p = F3(in.px[i], in.py[i], in.pz[i]), d = F3(in.dx[i], in.dy[i], in.dz[i]);
+    Info info = load_info(in.ix, in.iy, in.is, in.ig, in.scene_seed, in.info_t, i);
+    Coeff c = load_coeff(in.ctx, i);
+    Frame fr = ray_frame(P, d);
+    uint32_t seed = compute_seed(P, info);
+    if (what & SCN_EVAL_VALUE) { int id; float v = eval_value(P, c, fr, p, seed, id); out.val[i] = v; if (out.gp_id) out.gp_id[i] = id; }
+    if (what & SCN_EVAL_GRADIENT) { f3 g = eval_gradient(P, c, fr, p, in.t ? in.t[i] : 0.f, d, info, seed); out.gx[i] = g.x; out.gy[i] = g.y; out.gz[i] = g.z; }
+}
+
+struct CondArgs { const float *tv, *tgx, *tgy, *tgz; float *ctx[7]; };
+__global__ void __launch_bounds__(BLOCK) k_conditioning(const __grid_constant__ Params P, const EvalIn in, const CondArgs a, size_t n) {
+    size_t i = (size_t)blockIdx.x * BLOCK + threadIdx.x;
+    if (i >= n) return;
+    f3 p = F3(in.px[i], in.py[i], in.pz[i]), d = F3(in.dx[i], in.dy[i], in.dz[i]);
+    Info info = load_info(in.ix, in.iy, in.is, in.ig, in.scene_seed, in.info_t, i);
+    Coeff c; c.vs = 0.f; c.gs = F3(0.f, 0.f, 0.f); c.org = F3(0.f, 0.f, 0.f);
+    Frame fr = ray_frame(P, d);
+    conditioning(P, c, fr, p, d, a.tv[i], F3(a.tgx[i], a.tgy[i], a.tgz[i]), info);
+    a.ctx[0][i] = c.vs; a.ctx[1][i] = c.gs.x; a.ctx[2][i] = c.gs.y; a.ctx[3][i] = c.gs.z; a.ctx[4][i] = c.org.x; a.ctx[5][i] = c.org.y; a.ctx[6][i] = c.org.z;
+}
+
+struct Rays { const float *ox, *oy, *oz, *dx, *dy, *dz, *tmin, *tmax, *u; const uint32_t *px, *py, *spp, *seg; uint32_t scene_seed; };
+struct State { uint8_t *first_scatter; float *last_val, *lgx, *lgy, *lgz; int32_t *bounce, *last_gp_id; float *info_t; uint8_t *scheme; float *ctx[7]; };
+struct Samples { uint8_t *ok, *exited; float *t, *cont_t, *gx, *gy, *gz; int32_t *gp_id; uint8_t *scheme; float *weight; uint32_t *n_evals; };
+
+__device__ __forceinline__ RayState load_state(const State &s, const Rays &r, size_t i) {
+    RayState st;
+    st.first_scatter = s.first_scatter[i] != 0; st.last_val = s.last_val[i]; st.last_aniso = F3(s.lgx[i], s.lgy[i], s.lgz[i]);
+    st.bounce = s.bounce[i]; st.last_gp_id = s.last_gp_id[i]; st.scheme = SCN_SCHEME_UNI;
+    st.info = load_info(r.px, r.py, r.spp, r.seg, r.scene_seed, s.info_t, i);
+    st.c.vs = 0.f; st.c.gs = F3(0.f, 0.f, 0.f); st.c.org = F3(0.f, 0.f, 0.f);
+    return st;
+}
+
+__global__ void __launch_bounds__(BLOCK) k_sample_distance(const __grid_constant__ Params P, const Rays r, const State s, const Samples o, size_t n) {
+    size_t i = (size_t)blockIdx.x * BLOCK + threadIdx.x;
+    if (i >= n) return;
+    RayState st = load_state(s, r, i);
+    Sample sm;
+    medium_query(P, F3(r.ox[i], r.oy[i], r.oz[i]), F3(r.dx[i], r.dy[i], r.dz[i]), r.tmin[i], r.tmax[i], r.u[i], st, sm, false);
+    o.ok[i] = sm.ok; o.exited[i] = sm.exited; o.t[i] = sm.t; o.cont_t[i] = sm.cont_t;
+    o.gx[i] = sm.aniso.x; o.gy[i] = sm.aniso.y; o.gz[i] = sm.aniso.z;
+    o.gp_id[i] = sm.ok ? sm.gp_id : st.last_gp_id; o.scheme[i] = (uint8_t)sm.scheme; o.weight[i] = sm.weight;
+    if (o.n_evals) o.n_evals[i] = sm.n_evals;
+    s.first_scatter[i] = st.first_scatter; s.last_val[i] = st.last_val; s.lgx[i] = st.last_aniso.x; s.lgy[i] = st.last_aniso.y; s.lgz[i] = st.last_aniso.z;
+    s.bounce[i] = st.bounce; s.last_gp_id[i] = st.last_gp_id; s.info_t[i] = st.info.t; if (s.scheme) s.scheme[i] = (uint8_t)st.scheme;
+    if (s.ctx[0]) { s.ctx[0][i] = st.c.vs; s.ctx[1][i] = st.c.gs.x; s.ctx[2][i] = st.c.gs.y; s.ctx[3][i] = st.c.gs.z; s.ctx[4][i] = st.c.org.x; s.ctx[5][i] = st.c.org.y; s.ctx[6][i] = st.c.org.z; }
+}
+
+__global__ void __launch_bounds__(BLOCK) k_transmittance(const __grid_constant__ Params P, const Rays r, const State s, float *T, uint32_t *n_evals, size_t n) {
+    size_t i = (size_t)blockIdx.x * BLOCK + threadIdx.x;
+    if (i >= n) return;
+    RayState st = load_state(s, r, i);
+    Sample sm;
+    medium_query(P, F3(r.ox[i], r.oy[i], r.oz[i]), F3(r.dx[i], r.dy[i], r.dz[i]), r.tmin[i], r.tmax[i], r.u[i], st, sm, true);
+    T[i] = sm.weight;
+    if (n_evals) n_evals[i] = sm.n_evals;
+}
+
+struct NeeIn { const float *dx, *dy, *dz, *nx, *ny, *nz, *px, *py, *pz, *ts, *info_t; const uint32_t *ix, *iy, *is, *ig; uint32_t scene_seed; const float *ctx[7]; };
+__global__ void __launch_bounds__(BLOCK) k_nee(const __grid_constant__ Params P, const NeeIn in, float *pdf, float *gx, float *gy, float *gz, size_t n) {
+    size_t i = (size_t)blockIdx.x * BLOCK + threadIdx.x;
+    if (i >= n) return;
+    f3 d = F3(in.dx[i], in.dy[i], in.dz[i]), nn = F3(in.nx[i], in.ny[i], in.nz[i]), p = F3(in.px[i], in.py[i], in.pz[i]);
+    Info info = load_info(in.ix, in.iy, in.is, in.ig, in.scene_seed, in.info_t, i);
+    Coeff c = load_coeff(in.ctx, i);
+    if (pdf) pdf[i] = nee_pdf(P, c, d, nn, p, in.ts ? in.ts[i] : 0.f, info);
+    if (gx) { Nee o; nee_shared(P, c, d, nn, p, info, o); gx[i] = o.dist * nn.x; gy[i] = o.dist * nn.y; gz[i] = o.dist * nn.z; }
+}
+
+__global__ void k_debug_hash4(const uint32_t *a, const uint32_t *b, const uint32_t *c, const uint32_t *d, uint32_t *out, size_t n) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) out[i] = xxhash32_4(a[i], b[i], c[i], d[i]);
+}
+__global__ void k_debug_pcg(const uint32_t *seed32, float *out, size_t n, int draws) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    Pcg g; g.seed32(seed32[i] - 1u); // seed32() adds the reference's +1u
+    for (int k = 0; k < draws; ++k) out[i * (size_t)draws + k] = g.next();
+}
+__global__ void k_debug_cell(const uint32_t *ci, const uint32_t *cj, const uint32_t *ck, uint32_t seed, uint32_t count, float *out, size_t n) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    Pcg g; g.seed32(xxhash32_4(ck[i], cj[i], ci[i], seed));
+    for (uint32_t k = 0; k < count; ++k) {
+        float z = g.next(), y = g.next(), x = g.next(), w = g.next() < 0.5f ? -1.f : 1.f;
+        float *o = out + (i * (size_t)count + k) * 4; o[0] = x; o[1] = y; o[2] = z; o[3] = w;
+    }
+}
+
+} // namespace scn
+
+// ---------------------------------------------------------------- C ABI
+using namespace scn;
+
+struct scn_medium {
+    scn_medium_desc desc;
+    Params P;
+    int device;
+    // staging arena of the *_host entry points
+    std::mutex mu;
+    cudaStream_t streams[3] = {nullptr, nullptr, nullptr};
+    char *arena[3] = {nullptr, nullptr, nullptr};
+    size_t arena_cap = 0;
+};
+
+static inline unsigned grid_for(size_t n) { return (unsigned)((n + BLOCK - 1) / BLOCK); }
+static int check_launch(const char *what) { cudaError_t e = cudaGetLastError(); if (e != cudaSuccess) return cuda_fail(e, what); return SCN_OK; }
+
+struct DeviceGuard {
+    int prev = -1; bool ok = true;
+    explicit DeviceGuard(int dev) { if (cudaGetDevice(&prev) != cudaSuccess) { ok = false; return; } if (prev != dev && cudaSetDevice(dev) != cudaSuccess) ok = false; }
+    ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+};
+
+extern "C" {
+
+const char *scn_last_error(void) { return g_err; }
+int scn_abi_version(void) { return SCN_ABI_VERSION; }
+int scn_desc_default(scn_medium_desc *d) { return desc_default(d); }
+int scn_desc_from_json(const char *json, scn_medium_desc *d) { return desc_from_json(json, d); }
+
+int scn_medium_create(const scn_medium_desc *desc, int device, scn_medium **out) {
+    if (!desc || !out) return set_error(SCN_EINVAL, "null argument");
+    *out = nullptr;
+    Params P;
+    if (int rc = params_from_desc(*desc, P)) return rc;
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count == 0) return set_error(SCN_ECUDA, "no CUDA device: this library has no CPU path (%s)", e != cudaSuccess ? cudaGetErrorString(e) : "0 devices");
+    if (device < 0 || device >= count) return set_error(SCN_EINVAL, "device %d out of range (0..%d)", device, count - 1);
+    scn_medium *m = new (std::nothrow) scn_medium();
+    if (!m) return set_error(SCN_ENOMEM, "out of memory");
+    m->desc = *desc; m->P = P; m->device = device;
+    *out = m;
+    return SCN_OK;
+}
+
+void scn_medium_destroy(scn_medium *m) {
+    if (!m) return;
+    {
+        DeviceGuard g(m->device);
+        for (int i = 0; i < 3; ++i) { if (m->arena[i]) cudaFree(m->arena[i]); if (m->streams[i]) cudaStreamDestroy(m->streams[i]); }
+    }
+    delete m;
+}
+
+static void to_eval_in(const scn_eval_in *in, EvalIn &k) {
+    k.px = in->px; k.py = in->py; k.pz = in->pz; k.dx = in->dx; k.dy = in->dy; k.dz = in->dz; k.t = in->t; k.info_t = in->info_t;
+    k.ix = in->pix_x; k.iy = in->pix_y; k.is = in->pix_spp; k.ig = in->pix_seg; k.scene_seed = in->scene_seed; k.noise_seed = in->noise_seed;
+    bool all = true; for (int i = 0; i < 7; ++i) all = all && in->ctx[i];
+    for (int i = 0; i < 7; ++i) k.ctx[i] = all ? in->ctx[i] : nullptr;
+}
+
+int scn_eval_batch(const scn_medium *m, const scn_eval_in *in, const scn_eval_out *out, size_t n, int what, void *stream) {
+    if (!m || !in || !out) return set_error(SCN_EINVAL, "null argument");
+    if (!in->px || !in->py || !in->pz || !in->dx || !in->dy || !in->dz) return set_error(SCN_EINVAL, "eval: points and directions are required");
+    if (n == 0) return SCN_OK;
+    DeviceGuard g(m->device); if (!g.ok) return set_error(SCN_ECUDA, "cannot select device %d", m->device);
+    cudaStream_t s = (cudaStream_t)stream;
+    EvalIn ki; to_eval_in(in, ki);
+    EvalOut ko; ko.val = out->val; ko.gx = out->gx; ko.gy = out->gy; ko.gz = out->gz; ko.gp_id = out->gp_id;
+    if (what == SCN_EVAL_NOISE) {
+        if (!ko.val && !ko.gx) return set_error(SCN_EINVAL, "eval: no output requested");
+        if (ko.gx && (!ko.gy || !ko.gz)) return set_error(SCN_EINVAL, "eval: gx, gy, gz go together");
+        if (fast_noise3d_supported(m->P) && ko.val && ko.gx) launch_fast_noise3d(m->P, ki.px, ki.py, ki.pz, ki.dx, ki.dy, ki.dz, ki.noise_seed, ko.val, ko.gx, ko.gy, ko.gz, n, s);
+        else k_eval_noise<<<grid_for(n), BLOCK, 0, s>>>(m->P, ki, ko, n);
+        return check_launch("k_eval_noise");
+    }
+    if (!(what & (SCN_EVAL_VALUE | SCN_EVAL_GRADIENT)) || (what & ~(SCN_EVAL_VALUE | SCN_EVAL_GRADIENT))) return set_error(SCN_EINVAL, "eval: bad `what` %d", what);
+    if ((what & SCN_EVAL_VALUE) && !ko.val) return set_error(SCN_EINVAL, "eval: val output required");
+    if ((what & SCN_EVAL_GRADIENT) && (!ko.gx || !ko.gy || !ko.gz)) return set_error(SCN_EINVAL, "eval: gradient outputs required");
+    k_eval<<<grid_for(n), BLOCK, 0, s>>>(m->P, ki, ko, n, what);
+    return check_launch("k_eval");
+}
+
+int scn_conditioning_batch(const scn_medium *m, const scn_eval_in *in, const float *tv, const float *tgx, const float *tgy, const float *tgz,
+                           float *const ctx_out[7], size_t n, void *stream) {
+    if (!m || !in || !tv || !tgx || !tgy || !tgz || !ctx_out) return set_error(SCN_EINVAL, "null argument");
+    for (int i = 0; i < 7; ++i) if (!ctx_out[i]) return set_error(SCN_EINVAL, "conditioning: all 7 coefficient outputs are required");
+    if (n == 0) return SCN_OK;
+    DeviceGuard g(m->device); if (!g.ok) return set_error(SCN_ECUDA, "cannot select device %d", m->device);
+    EvalIn ki; to_eval_in(in, ki);
+    CondArgs a; a.tv = tv; a.tgx = tgx; a.tgy = tgy; a.tgz = tgz; for (int i = 0; i < 7; ++i) a.ctx[i] = ctx_out[i];
+    k_conditioning<<<grid_for(n), BLOCK, 0, (cudaStream_t)stream>>>(m->P, ki, a, n);
+    return check_launch("k_conditioning");
+}
+
+static int to_rays(const scn_rays *r, Rays &k) {
+    if (!r->ox || !r->oy || !r->oz || !r->dx || !r->dy || !r->dz || !r->tmin || !r->tmax || !r->u) return set_error(SCN_EINVAL, "rays: origin, direction, tmin, tmax and u are required");
+    k.ox = r->ox; k.oy = r->oy; k.oz = r->oz; k.dx = r->dx; k.dy = r->dy; k.dz = r->dz; k.tmin = r->tmin; k.tmax = r->tmax; k.u = r->u;
+    k.px = r->px; k.py = r->py; k.spp = r->spp; k.seg = r->segment; k.scene_seed = r->scene_seed;
+    return SCN_OK;
+}
+static int to_state(const scn_state *s, State &k) {
+    if (!s->first_scatter || !s->last_val || !s->last_gx || !s->last_gy || !s->last_gz || !s->bounce || !s->last_gp_id || !s->info_t)
+        return set_error(SCN_EINVAL, "state: first_scatter, last_val, last_g{x,y,z}, bounce, last_gp_id and info_t are required");
+    k.first_scatter = s->first_scatter; k.last_val = s->last_val; k.lgx = s->last_gx; k.lgy = s->last_gy; k.lgz = s->last_gz;
+    k.bounce = s->bounce; k.last_gp_id = s->last_gp_id; k.info_t = s->info_t; k.scheme = s->scheme;
+    bool all = true; for (int i = 0; i < 7; ++i) all = all && s->ctx[i];
+    for (int i = 0; i < 7; ++i) k.ctx[i] = all ? s->ctx[i] : nullptr;
+    return SCN_OK;
+}
+
+int scn_sample_distance_batch(const scn_medium *m, const scn_rays *rays, const scn_state *state, const scn_samples *out, size_t n, void *stream) {
+    if (!m || !rays || !state || !out) return set_error(SCN_EINVAL, "null argument");
+    if (!out->ok || !out->exited || !out->t || !out->continued_t || !out->gx || !out->gy || !out->gz || !out->gp_id || !out->scheme || !out->weight)
+        return set_error(SCN_EINVAL, "samples: every output but n_evals is required");
+    Rays kr; State ks;
+    if (int rc = to_rays(rays, kr)) return rc;
+    if (int rc = to_state(state, ks)) return rc;
+    if (n == 0) return SCN_OK;
+    DeviceGuard g(m->device); if (!g.ok) return set_error(SCN_ECUDA, "cannot select device %d", m->device);
+    Samples ko; ko.ok = out->ok; ko.exited = out->exited; ko.t = out->t; ko.cont_t = out->continued_t; ko.gx = out->gx; ko.gy = out->gy; ko.gz = out->gz;
+    ko.gp_id = out->gp_id; ko.scheme = out->scheme; ko.weight = out->weight; ko.n_evals = out->n_evals;
+    k_sample_distance<<<grid_for(n), BLOCK, 0, (cudaStream_t)stream>>>(m->P, kr, ks, ko, n);
+    return check_launch("k_sample_distance");
+}
+
+static int transmittance_impl(const scn_medium *m, const scn_rays *rays, const scn_state *state, float *T, uint32_t *n_evals, size_t n, cudaStream_t s) {
+    Rays kr; State ks;
+    if (int rc = to_rays(rays, kr)) return rc;
+    if (int rc = to_state(state, ks)) return rc;
+    if (n == 0) return SCN_OK;
+    k_transmittance<<<grid_for(n), BLOCK, 0, s>>>(m->P, kr, ks, T, n_evals, n);
+    return check_launch("k_transmittance");
+}
+int scn_transmittance_batch(const scn_medium *m, const scn_rays *rays, const scn_state *state, float *T_out, size_t n, void *stream) {
+    if (!m || !rays || !state || !T_out) return set_error(SCN_EINVAL, "null argument");
+    DeviceGuard g(m->device); if (!g.ok) return set_error(SCN_ECUDA, "cannot select device %d", m->device);
+    return transmittance_impl(m, rays, state, T_out, nullptr, n, (cudaStream_t)stream);
+}
+
+static int nee_impl(const scn_medium *m, const scn_nee_in *in, float *pdf, float *gx, float *gy, float *gz, size_t n, void *stream) {
+    if (!m || !in) return set_error(SCN_EINVAL, "null argument");
+    if (!in->dx || !in->dy || !in->dz || !in->nx || !in->ny || !in->nz || !in->px || !in->py || !in->pz) return set_error(SCN_EINVAL, "nee: direction, normal and position are required");
+    if (n == 0) return SCN_OK;
+    DeviceGuard g(m->device); if (!g.ok) return set_error(SCN_ECUDA, "cannot select device %d", m->device);
+    NeeIn k; k.dx = in->dx; k.dy = in->dy; k.dz = in->dz; k.nx = in->nx; k.ny = in->ny; k.nz = in->nz; k.px = in->px; k.py = in->py; k.pz = in->pz;
+    k.ts = in->t_segment; k.info_t = in->info_t; k.ix = in->pix_x; k.iy = in->pix_y; k.is = in->pix_spp; k.ig = in->pix_seg; k.scene_seed = in->scene_seed;
+    bool all = true; for (int i = 0; i < 7; ++i) all = all && in->ctx[i];
+    for (int i = 0; i < 7; ++i) k.ctx[i] = all ? in->ctx[i] : nullptr;
+    k_nee<<<grid_for(n), BLOCK, 0, (cudaStream_t)stream>>>(m->P, k, pdf, gx, gy, gz, n);
+    return check_launch("k_nee");
+}
+int scn_nee_pdf_batch(const scn_medium *m, const scn_nee_in *in, float *pdf_out, size_t n, void *stream) {
+    if (!pdf_out) return set_error(SCN_EINVAL, "null output");
+    return nee_impl(m, in, pdf_out, nullptr, nullptr, nullptr, n, stream);
+}
+int scn_nee_grad_batch(const scn_medium *m, const scn_nee_in *in, float *gx, float *gy, float *gz, size_t n, void *stream) {
+    if (!gx || !gy || !gz) return set_error(SCN_EINVAL, "null output");
+    return nee_impl(m, in, nullptr, gx, gy, gz, n, stream);
+}
+
+int scn_debug_hash4(const uint32_t *a, const uint32_t *b, const uint32_t *c, const uint32_t *d, uint32_t *out, size_t n, void *stream) {
+    if (!a || !b || !c || !d || !out) return set_error(SCN_EINVAL, "null argument");
+    if (n == 0) return SCN_OK;
+    k_debug_hash4<<<grid_for(n), BLOCK, 0, (cudaStream_t)stream>>>(a, b, c, d, out, n);
+    return check_launch("k_debug_hash4");
+}
+int scn_debug_pcg_stream(const uint32_t *seed32, float *out, size_t n, int draws, void *stream) {
+    if (!seed32 || !out || draws < 0) return set_error(SCN_EINVAL, "bad argument");
+    if (n == 0) return SCN_OK;
+    k_debug_pcg<<<grid_for(n), BLOCK, 0, (cudaStream_t)stream>>>(seed32, out, n, draws);
+    return check_launch("k_debug_pcg");
+}
+int scn_debug_cell_impulses(const uint32_t *ci, const uint32_t *cj, const uint32_t *ck, uint32_t seed, uint32_t count, float *out, size_t n, void *stream) {
+    if (!ci || !cj || !ck || !out) return set_error(SCN_EINVAL, "null argument");
+    if (n == 0) return SCN_OK;
+    k_debug_cell<<<grid_for(n), BLOCK, 0, (cudaStream_t)stream>>>(ci, cj, ck, seed, count, out, n);
+    return check_launch("k_debug_cell");
+}
+
+// ---------------------------------------------------------------- host-buffer entry points (the thin Tungsten shim calls these)
+// Chunks of the batch travel host -> device -> kernel -> host on three round-robin streams, so the H2D copy of
+// chunk k+1, the kernel of chunk k and the D2H copy of chunk k-1 overlap.  The arena is grown once and reused.
+static int ensure_arena(scn_medium *m, size_t bytes_per_slot) {
+    for (int i = 0; i < 3; ++i) if (!m->streams[i]) SCN_CUDA(cudaStreamCreateWithFlags(&m->streams[i], cudaStreamNonBlocking));
+    if (bytes_per_slot <= m->arena_cap) return SCN_OK;
+    for (int i = 0; i < 3; ++i) { if (m->arena[i]) { SCN_CUDA(cudaFree(m->arena[i])); m->arena[i] = nullptr; } }
+    m->arena_cap = 0;
+    for (int i = 0; i < 3; ++i) SCN_CUDA(cudaMalloc((void **)&m->arena[i], bytes_per_slot));
+    m->arena_cap = bytes_per_slot;
+    return SCN_OK;
+}
+constexpr size_t HOST_CHUNK = (size_t)1 << 21; // queries per pipeline stage
+
+} // extern "C"
+struct Carver { // carves aligned sub-buffers out of one arena slot
+    char *base; size_t off = 0;
+    template <typename T> T *take(size_t count) { T *p = (T *)(base + off); off += (count * sizeof(T) + 255) & ~(size_t)255; return p; }
+};
+template <typename T> static cudaError_t h2d(T *dst, const T *src, size_t first, size_t count, cudaStream_t s) { return cudaMemcpyAsync(dst, src + first, count * sizeof(T), cudaMemcpyHostToDevice, s); }
+template <typename T> static cudaError_t d2h(T *dst, size_t first, const T *src, size_t count, cudaStream_t s) { return cudaMemcpyAsync(dst + first, src, count * sizeof(T), cudaMemcpyDeviceToHost, s); }
+extern "C" {
+
+int scn_eval_batch_host(scn_medium *m, const scn_eval_in *in, const scn_eval_out *out, size_t n, int what) {
+    if (!m || !in || !out) return set_error(SCN_EINVAL, "null argument");
+    if (!in->px || !in->py || !in->pz || !in->dx || !in->dy || !in->dz) return set_error(SCN_EINVAL, "eval: points and directions are required");
+    if (n == 0) return SCN_OK;
+    std::lock_guard<std::mutex> lock(m->mu);
+    DeviceGuard g(m->device); if (!g.ok) return set_error(SCN_ECUDA, "cannot select device %d", m->device);
+    size_t chunk = n < HOST_CHUNK ? n : HOST_CHUNK;
+    size_t per = ((chunk * 4 + 255) & ~(size_t)255) * 32; // <= 32 arrays of 4-byte elements
+    if (int rc = ensure_arena(m, per)) return rc;
+    bool has_ctx = true; for (int i = 0; i < 7; ++i) has_ctx = has_ctx && in->ctx[i];
+    int slot = 0;
+    for (size_t b = 0; b < n; b += chunk, slot = (slot + 1) % 3) {
+        size_t c = n - b < chunk ? n - b : chunk;
+        cudaStream_t s = m->streams[slot];
+        Carver cv{m->arena[slot]};
+        scn_eval_in di = *in; scn_eval_out dd = *out;
+        float *f;
+#define IN_F(field) if (in->field) { f = cv.take<float>(c); SCN_CUDA(h2d(f, in->field, b, c, s)); di.field = f; }
+#define IN_U(field) if (in->field) { uint32_t *q = cv.take<uint32_t>(c); SCN_CUDA(h2d(q, in->field, b, c, s)); di.field = q; }
+        IN_F(px) IN_F(py) IN_F(pz) IN_F(dx) IN_F(dy) IN_F(dz) IN_F(t) IN_F(info_t) IN_U(pix_x) IN_U(pix_y) IN_U(pix_spp) IN_U(pix_seg)
+        for (int i = 0; i < 7; ++i) { di.ctx[i] = nullptr; if (has_ctx) { f = cv.take<float>(c); SCN_CUDA(h2d(f, in->ctx[i], b, c, s)); di.ctx[i] = f; } }
+#undef IN_F
+#undef IN_U
+        if (out->val) dd.val = cv.take<float>(c);
+        if (out->gx) dd.gx = cv.take<float>(c);
+        if (out->gy) dd.gy = cv.take<float>(c);
+        if (out->gz) dd.gz = cv.take<float>(c);
+        if (out->gp_id) dd.gp_id = cv.take<int32_t>(c);
+        if (int rc = scn_eval_batch(m, &di, &dd, c, what, s)) return rc;
+        if (out->val) SCN_CUDA(d2h(out->val, b, dd.val, c, s));
+        if (out->gx) SCN_CUDA(d2h(out->gx, b, dd.gx, c, s));
+        if (out->gy) SCN_CUDA(d2h(out->gy, b, dd.gy, c, s));
+        if (out->gz) SCN_CUDA(d2h(out->gz, b, dd.gz, c, s));
+        if (out->gp_id) SCN_CUDA(d2h(out->gp_id, b, dd.gp_id, c, s));
+    }
+    for (int i = 0; i < 3; ++i) SCN_CUDA(cudaStreamSynchronize(m->streams[i]));
+    return SCN_OK;
+}
+
+static int query_host(scn_medium *m, const scn_rays *rays, const scn_state *state, const scn_samples *out, float *T_out, size_t n) {
+    if (!m || !rays || !state) return set_error(SCN_EINVAL, "null argument");
+    Rays kr; State ks;
+    if (int rc = to_rays(rays, kr)) return rc;
+    if (int rc = to_state(state, ks)) return rc;
+    if (out && (!out->ok || !out->exited || !out->t || !out->continued_t || !out->gx || !out->gy || !out->gz || !out->gp_id || !out->scheme || !out->weight))
+        return set_error(SCN_EINVAL, "samples: every output but n_evals is required");
+    if (n == 0) return SCN_OK;
+    std::lock_guard<std::mutex> lock(m->mu);
+    DeviceGuard g(m->device); if (!g.ok) return set_error(SCN_ECUDA, "cannot select device %d", m->device);
+    size_t chunk = n < HOST_CHUNK ? n : HOST_CHUNK;
+    size_t per = ((chunk * 4 + 255) & ~(size_t)255) * 48;
+    if (int rc = ensure_arena(m, per)) return rc;
+    int slot = 0;
+    for (size_t b = 0; b < n; b += chunk, slot = (slot + 1) % 3) {
+        size_t c = n - b < chunk ? n - b : chunk;
+        cudaStream_t s = m->streams[slot];
+        Carver cv{m->arena[slot]};
+        scn_rays dr = *rays; scn_state ds = *state;
+        float *f; uint32_t *q; uint8_t *u8; int32_t *i32;
+#define RAY_F(field) f = cv.take<float>(c); SCN_CUDA(h2d(f, rays->field, b, c, s)); dr.field = f;
+#define RAY_U(field) if (rays->field) { q = cv.take<uint32_t>(c); SCN_CUDA(h2d(q, rays->field, b, c, s)); dr.field = q; }
+        RAY_F(ox) RAY_F(oy) RAY_F(oz) RAY_F(dx) RAY_F(dy) RAY_F(dz) RAY_F(tmin) RAY_F(tmax) RAY_F(u) RAY_U(px) RAY_U(py) RAY_U(spp) RAY_U(segment)
+#undef RAY_F
+#undef RAY_U
+        u8 = cv.take<uint8_t>(c); SCN_CUDA(h2d(u8, (const uint8_t *)state->first_scatter, b, c, s)); ds.first_scatter = u8;
+#define ST_F(field) f = cv.take<float>(c); SCN_CUDA(h2d(f, (const float *)state->field, b, c, s)); ds.field = f;
+        ST_F(last_val) ST_F(last_gx) ST_F(last_gy) ST_F(last_gz) ST_F(info_t)
+#undef ST_F
+        i32 = cv.take<int32_t>(c); SCN_CUDA(h2d(i32, (const int32_t *)state->bounce, b, c, s)); ds.bounce = i32;
+        i32 = cv.take<int32_t>(c); SCN_CUDA(h2d(i32, (const int32_t *)state->last_gp_id, b, c, s)); ds.last_gp_id = i32;
+        ds.scheme = state->scheme ? cv.take<uint8_t>(c) : nullptr;
+        bool has_ctx = ks.ctx[0] != nullptr;
+        for (int i = 0; i < 7; ++i) ds.ctx[i] = has_ctx ? cv.take<float>(c) : nullptr;
+        if (out) {
+            scn_samples dd = *out;
+            dd.ok = cv.take<uint8_t>(c); dd.exited = cv.take<uint8_t>(c); dd.t = cv.take<float>(c); dd.continued_t = cv.take<float>(c);
+            dd.gx = cv.take<float>(c); dd.gy = cv.take<float>(c); dd.gz = cv.take<float>(c); dd.gp_id = cv.take<int32_t>(c); dd.scheme = cv.take<uint8_t>(c);
+            dd.weight = cv.take<float>(c); dd.n_evals = out->n_evals ? cv.take<uint32_t>(c) : nullptr;
+            if (int rc = scn_sample_distance_batch(m, &dr, &ds, &dd, c, s)) return rc;
+            SCN_CUDA(d2h(out->ok, b, dd.ok, c, s)); SCN_CUDA(d2h(out->exited, b, dd.exited, c, s)); SCN_CUDA(d2h(out->t, b, dd.t, c, s));
+            SCN_CUDA(d2h(out->continued_t, b, dd.continued_t, c, s)); SCN_CUDA(d2h(out->gx, b, dd.gx, c, s)); SCN_CUDA(d2h(out->gy, b, dd.gy, c, s));
+            SCN_CUDA(d2h(out->gz, b, dd.gz, c, s)); SCN_CUDA(d2h(out->gp_id, b, dd.gp_id, c, s)); SCN_CUDA(d2h(out->scheme, b, dd.scheme, c, s));
+            SCN_CUDA(d2h(out->weight, b, dd.weight, c, s)); if (out->n_evals) SCN_CUDA(d2h(out->n_evals, b, dd.n_evals, c, s));
+            // the state is read-modify-write
+            SCN_CUDA(d2h(state->first_scatter, b, ds.first_scatter, c, s)); SCN_CUDA(d2h(state->last_val, b, ds.last_val, c, s));
+            SCN_CUDA(d2h(state->last_gx, b, ds.last_gx, c, s)); SCN_CUDA(d2h(state->last_gy, b, ds.last_gy, c, s)); SCN_CUDA(d2h(state->last_gz, b, ds.last_gz, c, s));
+            SCN_CUDA(d2h(state->bounce, b, ds.bounce, c, s)); SCN_CUDA(d2h(state->last_gp_id, b, ds.last_gp_id, c, s)); SCN_CUDA(d2h(state->info_t, b, ds.info_t, c, s));
+            if (state->scheme) SCN_CUDA(d2h(state->scheme, b, ds.scheme, c, s));
+            if (has_ctx) for (int i = 0; i < 7; ++i) SCN_CUDA(d2h(state->ctx[i], b, ds.ctx[i], c, s));
+        } else {
+            float *T = cv.take<float>(c);
+            if (int rc = transmittance_impl(m, &dr, &ds, T, nullptr, c, s)) return rc;
+            SCN_CUDA(d2h(T_out, b, T, c, s));
+        }
+    }
+    for (int i = 0; i < 3; ++i) SCN_CUDA(cudaStreamSynchronize(m->streams[i]));
+    return SCN_OK;
+}
+int scn_sample_distance_batch_host(scn_medium *m, const scn_rays *rays, const scn_state *state, const scn_samples *out, size_t n) {
+    if (!out) return set_error(SCN_EINVAL, "null argument");
+    return query_host(m, rays, state, out, nullptr, n);
+}
+int scn_transmittance_batch_host(scn_medium *m, const scn_rays *rays, const scn_state *state, float *T_out, size_t n) {
+    if (!T_out) return set_error(SCN_EINVAL, "null argument");
+    return query_host(m, rays, state, nullptr, T_out, n);
+}
+
+} // extern "C"

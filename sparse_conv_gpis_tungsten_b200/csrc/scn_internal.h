@@ -1,0 +1,70 @@
+// scn_internal.h — shared between the host side of the library (scn_json.cpp, scn_api.cu) and the kernels.
+#ifndef SCN_INTERNAL_H_
+#define SCN_INTERNAL_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#include "../../include/scn.h"
+
+namespace scn {
+
+int set_error(int code, const char *fmt, ...);
+int desc_default(scn_medium_desc *d);
+int desc_from_json(const char *text, scn_medium_desc *d);
+
+// Multi-resolution levels k in [LVL_MIN, LVL_MIN + LVL_COUNT): scale = powf(2.5f, k) and the seed offset
+// floor(logf(scale)/logf(2.5f)) come out of the HOST libm (the reference derives an integer seed offset and
+// the grid scaling from them, math/SparseConvolutionNoise.cpp:60-70,252,300,328), never out of device libm.
+constexpr int LVL_MIN = -20;
+constexpr int LVL_COUNT = 41;
+
+// A procedural field with the per-call constants of the reference hoisted to the host (math/GPFunctions.cpp:53-138).
+struct FieldK {
+    int32_t type, _pad;
+    double val[3];
+    double la[2], lb[2], scale[2], off[2]; // [0] first ramp, [1] second ramp of bottom_top_left_right
+};
+
+// Everything a kernel needs, derived once from scn_medium_desc in scn_medium_create (device copy lives in
+// constant-bank kernel parameters: the struct is passed by value as a __grid_constant__).
+struct Params {
+    // SparseConvolutionNoiseRealization flags (math/SparseConvolutionNoise.cpp:8-37)
+    uint32_t n_imp;            // uint(impulseDensity)
+    float density;             // impulseDensity as given (feeds the variance normalisation untruncated)
+    uint32_t global_seed;
+    int32_t single_realization, iso3d, sampling_1d, ctx, corr_xy, activate_conditioning, scheme;
+    int32_t stationary, multires;
+    int32_t surf_vol_sep; float surf_vol_thresh;
+    // medium (media/SparseConvolutionNoiseMedium.cpp, media/GaussianProcessMedium.cpp:152-158)
+    float step_size; uint32_t min_step; int32_t max_bounces; int32_t absorption_only; float sigma_s_over_t;
+    // squared-exponential kernel (math/GPFunctions.cpp:654-679)
+    float sigma, kernel_scale;
+    float l_aniso[3], l_aniso_inv[3];
+    float l_aniso_max, ls_max;
+    // radii / normalisation that do not depend on the query point
+    float R_iso;               // splattingKernelRadius(true, .)
+    float R_world;             // splattingKernelRadius(false, 1) (stationary and brute-force non-stationary)
+    float nf_iso;              // sqrt(variance3D(isIdentity=true))            (stationary / multires)
+    float nf_world;            // sqrt(variance3D(isIdentity=false, gs=world)) (stationary)
+    float nf_1d;               // sqrt(variance1D(localScale=1))               (stationary / multires)
+    float world_scale;         // worldSamplingSpatialScale()
+    int32_t add_seed_world;    // floor(log(world_scale)/log(2.5)) on the host
+    // multi-resolution tables
+    float lvl_scale[LVL_COUNT];
+    int32_t lvl_add_seed[LVL_COUNT];
+    float lvl_R_world[LVL_COUNT];
+    float lvl_nf_world[LVL_COUNT];
+    // GP
+    int32_t gp_id, has_mean_add, id_add, _pad;
+    scn_mean_desc mean, mean_add;
+    FieldK ls, var;
+    float log_base;            // logf(2.5f) from the host libm
+    int32_t _pad2;
+};
+
+int params_from_desc(const scn_medium_desc &d, Params &p);
+
+} // namespace scn
+
+#endif
