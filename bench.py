@@ -1,0 +1,315 @@
+#!/usr/bin/env python
+"""bench.py — headline benchmark of the GPIS medium-query path (BASELINE.json metric, configs[1]).
+
+  python bench.py --gpus N --steps K --warmup W            # this repo's CUDA path (one process per GPU under torchrun)
+  python bench.py --impl reference --gpus N --steps K ...   # the reference's own CPU code on the host cores
+
+Workload: 2^26 points uniform in [-8,8]^3 (seed 1234), unit directions (seed 1235); medium =
+stationary squared-exponential sigma=1 lengthScale=1 aniso=[1,1,1] localScale=3, single_realization, seed 1,
+impulse_density 3, isotropic-ray sampling; one step = value+gradient of evaluateNoise3D at every point.
+`value` = noise evaluations / s with inputs resident in HBM (CUDA events on the launching stream);
+`e2e` = the same through the C ABI's host-buffer entry point (pinned host memory, H2D + kernel + D2H timed);
+`roofline` = SURVEY §8(d) algorithmic lane-ops per evaluation x evaluations / s against the FP32 issue peak at the
+clock measured during the run (the path is issue-bound: 40 B and ~6e3 lane-ops per evaluation);
+`cpu_baseline` = the compiled reference (oracle/_ref) or the oracle port on the host cores, bounded sample.
+Each rank of an N-GPU run owns its own 2^26 points (weak scaling, no data-path collective).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+N_POINTS = 1 << 26
+DENSITY = 3
+ISO = True
+METRIC = "noise_evals_per_sec"
+UNIT = "evals/s"
+
+
+def w_issue(n):  # SURVEY.md §8(d), frozen before the first measurement
+    return 681 + 1803 * n
+
+
+def w_flop(n):
+    return 80 + 412 * n
+
+
+def workload_name(density=DENSITY, iso=ISO):
+    return "C2 noise-eval microbench: 2^26 points, value+gradient, 3D, impulse_density=%d, %s sampling" % (density, "isotropic-ray" if iso else "world-space")
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index = index
+        self.stop_flag = threading.Event()
+        self.rows = []
+
+    def run(self):
+        q = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+        while not self.stop_flag.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + q, "--format=csv,noheader,nounits"],
+                                     capture_output=True, text=True, timeout=5).stdout.strip()
+                if out:
+                    self.rows.append([x.strip() for x in out.split(",")])
+            except Exception:
+                pass
+            self.stop_flag.wait(0.1)
+
+    def summary(self):
+        sm = [float(r[0]) for r in self.rows if r and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) > 1 and r[1].replace(".", "").isdigit()]
+        reasons = set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            for k, nme in enumerate(names):
+                if len(r) > 3 + k and r[3 + k].lower().startswith("active"):
+                    reasons.add(nme)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def cpu_impl(medium_json, threads):
+    import support as S
+    kind = "ref" if S.have_ref() else "orc"
+    return S.CpuImpl(kind, medium_json, threads=threads), ("reference" if kind == "ref" else "port")
+
+
+def host_points(n, offset=0):
+    """The first n points of the seeded stream, generated on the host (numpy mirrors of seeds 1234/1235)."""
+    import support as S
+    return S.eval_points(n, seed=1234 + 2 * offset)
+
+
+def time_cpu(impl, p, d, repeats=1):
+    best = None
+    for _ in range(repeats):
+        t0 = time.perf_counter()
+        impl.eval_noise(p, d, 1)
+        dt = time.perf_counter() - t0
+        best = dt if best is None else min(best, dt)
+    return best
+
+
+def run_reference(args):
+    """The reference arm: the reference's own CPU implementation of the path (oracle/_ref when it was compiled from
+    /root/reference, else the oracle port), all host threads, bounded sample of the same workload per step."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    import support as S
+    threads = os.cpu_count() or 1
+    mj = S.microbench_medium(DENSITY, ISO)
+    impl, kind = cpu_impl(mj, threads)
+    sample = 1 << 21
+    p, d = host_points(sample)
+    for _ in range(max(args.warmup, 1)):
+        impl.eval_noise(p[: sample // 8], d[: sample // 8], 1)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        impl.eval_noise(p, d, 1)
+    dt = time.perf_counter() - t0
+    v = sample * args.steps / dt
+    line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": workload_name(), "points_per_step": sample, "note": "bounded sample of the 2^26-point workload per step"},
+            "cpu_baseline": {"value": v, "unit": UNIT, "cores": threads, "kind": kind, "sample": "2^21 of the 2^26 points per step, value+gradient"},
+            "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
+    print(json.dumps(line))
+    return 0
+
+
+def run_gpu(args):
+    import torch
+    import torch.distributed as dist
+    import support as S
+    from sparse_conv_gpis_tungsten_b200 import SparseConvolutionNoiseMedium, new_state
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device — this repo has no CPU path (use --impl reference for the CPU baseline)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    n = args.points
+    mj = S.microbench_medium(DENSITY, ISO)
+    med = SparseConvolutionNoiseMedium.from_json(mj, device=local)
+    gen = torch.Generator(device=dev)
+    gen.manual_seed(1234 + 2 * rank)  # every rank owns its own 2^26 points
+    P = [(torch.rand(n, generator=gen, device=dev) * 16 - 8) for _ in range(3)]
+    gen.manual_seed(1235 + 2 * rank)
+    Dm = torch.randn(3, n, generator=gen, device=dev)
+    Dm = Dm / Dm.norm(dim=0, keepdim=True)
+    D = [Dm[0].contiguous(), Dm[1].contiguous(), Dm[2].contiguous()]
+    del Dm
+    outs = [torch.empty(n, device=dev) for _ in range(4)]
+    stream = torch.cuda.current_stream()
+
+    def step():
+        med.eval_noise_into(P, D, 1, outs, stream=stream)
+
+    for _ in range(max(args.warmup, 3)):
+        step()
+    torch.cuda.synchronize()
+    sampler = ClockSampler(local)
+    sampler.start()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    for _ in range(args.steps):
+        step()
+    e1.record(stream)
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    ms = e0.elapsed_time(e1)
+    sampler.stop_flag.set(); sampler.join(timeout=3)
+    t = torch.tensor([ms], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_max = float(t.item())
+    value = world * n * args.steps / (ms_max * 1e-3)
+
+    # ---- end to end through the host-buffer entry point (rank-local; max over ranks)
+    ne = min(n, args.e2e_points)
+    hp = [x[:ne].cpu().pin_memory() for x in P]
+    hd = [x[:ne].cpu().pin_memory() for x in D]
+    ho = [torch.empty(ne, pin_memory=True) for _ in range(4)]
+    med.eval_noise_into(hp, hd, 1, ho)  # grows the staging arena once
+    med.eval_noise_into(hp, hd, 1, ho)
+    if world > 1:
+        dist.barrier()
+    e2e_steps = max(1, min(args.steps, 3))
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        med.eval_noise_into(hp, hd, 1, ho)
+    torch.cuda.synchronize()
+    e2e_s = time.perf_counter() - t0
+    te = torch.tensor([e2e_s], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(te, op=dist.ReduceOp.MAX)
+    e2e_value = world * ne * e2e_steps / float(te.item())
+    same = all(torch.equal(a, b[:ne].cpu()) for a, b in zip(ho, outs))
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return 0
+
+    clocks = sampler.summary()
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    props = torch.cuda.get_device_properties(local)
+    sms = props.multi_processor_count
+    f_mhz = clocks["sm_mhz"] or peaks.get("sm_max_mhz") or 1965.0
+    per_gpu = value / world
+    issue_peak = sms * 4 * 32 * f_mhz * 1e6            # lane-ops / s at the clock seen during the run
+    fp32_peak = sms * 128 * 2 * f_mhz * 1e6
+    ach_issue = per_gpu * w_issue(DENSITY)
+    hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
+    roofline = {"bound": "fp32-issue", "achieved": ach_issue / 1e12, "peak": issue_peak / 1e12, "unit": "Tlane-op/s", "frac": ach_issue / issue_peak,
+                "traffic": None, "kernel": "k_fast_noise3d<ISO>", "avg_launch_ms": ms_max / args.steps,
+                "algorithmic": {"lane_ops_per_eval": w_issue(DENSITY), "flops_per_eval": w_flop(DENSITY), "bytes_per_eval": 40, "evals_per_launch": n},
+                "fp32_flops": {"achieved": per_gpu * w_flop(DENSITY) / 1e12, "peak": fp32_peak / 1e12, "unit": "TFLOP/s", "frac": per_gpu * w_flop(DENSITY) / fp32_peak},
+                "hbm": {"achieved": per_gpu * 40 / 1e9, "peak": hbm_peak, "unit": "GB/s", "frac": per_gpu * 40 / 1e9 / hbm_peak,
+                        "peak_source": "measured (MEASURED_PEAKS.json)" if "hbm_gbs" in peaks else "fallback"},
+                "peak_source": "SMs x 4 schedulers x 32 lanes x SM clock sampled during the timed region (SURVEY.md 8(d)); sm_count=%d, MHz=%.0f" % (sms, f_mhz)}
+
+    # ---- extras: density sweep, world space, medium queries / s (configs[0]-style rays); one pass each, outside the timed region
+    extra = {"e2e_matches_device": bool(same)}
+    if not args.no_extras:
+        sweep = {}
+        for iso in (True, False):
+            for dens in (1, 2, 4, 8, 16, 32, 64):
+                m2 = SparseConvolutionNoiseMedium.from_json(S.microbench_medium(dens, iso), device=local)
+                m2.eval_noise_into(P, D, 1, outs, stream=stream)
+                torch.cuda.synchronize()
+                a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                a.record(stream); m2.eval_noise_into(P, D, 1, outs, stream=stream); b.record(stream); torch.cuda.synchronize()
+                ev = n / (a.elapsed_time(b) * 1e-3)
+                sweep["%s_N%d" % ("iso" if iso else "world", dens)] = {"evals_per_s": ev, "issue_frac": ev * w_issue(dens) / issue_peak}
+                m2.close()
+        extra["sweep"] = sweep
+        # medium queries: camera rays through the Appendix-A.1 cube (C1 medium), 2^20 rays
+        nq = 1 << 20
+        rays, st = S.camera_rays(nq, seed=11)
+        g = S.GpuImpl(S.MEDIA["c1_sphere_3d_none"], device=local)
+        r, s = g._rays_state(rays, st)
+        out = g.m.sample_distance(r, s, scene_seed=1, count_evals=True)
+        torch.cuda.synchronize()
+        r, s = g._rays_state(rays, st)
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record(stream); out = g.m.sample_distance(r, s, scene_seed=1, out=out, stream=stream); b.record(stream); torch.cuda.synchronize()
+        qs = a.elapsed_time(b) * 1e-3
+        ev = int(out["n_evals"].view(torch.int32).to(torch.int64).sum().item())
+        extra["medium_queries"] = {"workload": "C1 medium (sphere mean, SE, 3D iso, none/single), 2^20 camera rays, step 0.01",
+                                   "queries_per_s": nq / qs, "noise_evals_per_s": ev / qs, "evals_per_query": ev / nq}
+        g.close()
+
+    # ---- CPU baseline on this box's host cores (bounded sample)
+    threads = os.cpu_count() or 1
+    impl, kind = cpu_impl(mj, threads)
+    cs = 1 << 22
+    cp, cd = host_points(cs)
+    impl.eval_noise(cp[: cs // 16], cd[: cs // 16], 1)
+    cdt = time_cpu(impl, cp, cd, repeats=1)
+    cpu_v = cs / cdt
+    # and the checker: the same sample through the GPU must agree with the CPU arm
+    gp = [torch.from_numpy(np.ascontiguousarray(cp[:65536, j])).to(dev) for j in range(3)]
+    gd = [torch.from_numpy(np.ascontiguousarray(cd[:65536, j])).to(dev) for j in range(3)]
+    go = torch.stack(med.eval_noise(gp, gd, 1), 1).cpu().numpy()
+    want = impl.eval_noise(np.ascontiguousarray(cp[:65536]), np.ascontiguousarray(cd[:65536]), 1)
+    extra["parity_vs_cpu_max_rel_err"] = float(S.rel_err(go, want).max())
+
+    line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+            "ms_per_step": ms_max / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": workload_name(), "points_per_gpu_per_step": n, "impulse_density": DENSITY, "isotropic_3D_sampling": ISO,
+                       "l2": "inputs (%.1f GB) and outputs (%.1f GB) per step exceed the 126 MB L2" % (24 * n / 1e9, 16 * n / 1e9), "parallelism": "replicas x%d (weak)" % world},
+            "clocks": clocks, "roofline": roofline,
+            "cpu_baseline": {"value": cpu_v, "unit": UNIT, "cores": threads, "kind": kind, "sample": "first 2^22 of the 2^26 points, value+gradient, one pass"},
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": 24 * ne, "d2h_bytes_per_step": 16 * ne, "points_per_step": ne,
+                    "api": "scn_eval_batch_host (pinned host buffers, 3-stream chunked pipeline)"},
+            "gpu_launches": args.steps, "extra": extra}
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--points", type=int, default=N_POINTS)
+    ap.add_argument("--e2e-points", type=int, default=N_POINTS)
+    ap.add_argument("--no-extras", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+    return run_gpu(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

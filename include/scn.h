@@ -248,6 +248,11 @@ int scn_debug_pcg_stream(const uint32_t *seed32, float *out, size_t n, int draws
 int scn_debug_cell_impulses(const uint32_t *ci, const uint32_t *cj, const uint32_t *ck, uint32_t seed, uint32_t count,
                             float *out, size_t n, void *stream);
 
+/* per point: how many of the 27*N impulses generated by evaluateNoise3D pass the rejection test |p - p_i|^2 < 1
+ * (math/SparseConvolutionNoise.cpp:389) — stationary 3D media; proves the accepted-impulse SETS match the CPU's. */
+int scn_debug_accepted_counts(const scn_medium *m, const float *px, const float *py, const float *pz, const float *dx, const float *dy,
+                              const float *dz, uint32_t seed, uint32_t *out, size_t n, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

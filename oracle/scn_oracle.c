@@ -385,6 +385,7 @@ static v4 real_level_ratio(const real_t *r, v3 p) {
 }
 static inline int additional_seed(float kss) { return (int)floorf(logf(kss) / logf(2.5f)); } /* SCN:252,272,300,328 */
 
+static __thread uint32_t g_accept_count; /* impulses that passed |p - p_i|^2 < 1 since the last reset (test bookkeeping) */
 /* cell3D / noise3D (SCN:362-395) */
 static v4 real_cell3d(const real_t *r, v3 p_world, uint32_t ci, uint32_t cj, uint32_t ck, v3 p, uint32_t seed, float R, float kss) {
     pcg_t s; pcg_set_state(&s, (uint64_t)(uint32_t)(orc_xxhash32_4(ck, cj, ci, seed) + 1u));
@@ -394,6 +395,7 @@ static v4 real_cell3d(const real_t *r, v3 p_world, uint32_t ci, uint32_t cj, uin
         v3 pi = pcg_next3d(&s);
         float w = pcg_next1d(&s) < 0.5f ? -1.f : 1.f;
         v3 tp = v3_sub(p, pi);
+        if (v3_lensq(tp) < 1.0) g_accept_count++;
         if (v3_lensq(tp) < 1.0) sum = v4_add(sum, v4_scale(cov_kernel3d(r->m, v3_scale(p, R), v3_scale(pi, R), 0, r->m->d.isotropic_3d_sampling, kss, p_world), w));
     }
     return sum;
@@ -974,6 +976,13 @@ static void noise3d_range(void *c, size_t b, size_t e) {
 }
 int orc_eval_noise3d(orc_medium *m, size_t n, const float *p, const float *d, uint32_t seed, float *out4, int nthreads) {
     noise_args a = {m, p, d, seed, out4}; parallel_for(n, nthreads, noise3d_range, &a); return 0;
+}
+static void accept_range(void *c, size_t b, size_t e) {
+    noise_args *a = (noise_args *)c; real_t r; real_init(&r, a->m); uint32_t *out = (uint32_t *)a->out;
+    for (size_t i = b; i < e; ++i) { g_accept_count = 0; (void)real_eval_noise3d(&r, P3AT(a->p, i), P3AT(a->d, i), a->seed, 0); out[i] = g_accept_count; }
+}
+int orc_accepted_counts(orc_medium *m, size_t n, const float *p, const float *d, uint32_t seed, uint32_t *out, int nthreads) {
+    noise_args a = {m, p, d, seed, (float *)out}; parallel_for(n, nthreads, accept_range, &a); return 0;
 }
 static void noise1d_range(void *c, size_t b, size_t e) {
     noise_args *a = (noise_args *)c; real_t r; real_init(&r, a->m); float R = cov_radius(a->m, 1, 1.0f);

@@ -42,6 +42,8 @@ void orc_cell_impulses(uint32_t ci, uint32_t cj, uint32_t ck, uint32_t seed, uin
 void orc_multires_level(int k, float *scale, int *additional_seed);
 
 int orc_eval_noise3d(orc_medium *m, size_t n, const float *p, const float *d, uint32_t seed, float *out4, int nthreads);
+/* per point: how many of the 27*N generated impulses pass the rejection test inside evaluateNoise3D (both levels when multi-resolution) */
+int orc_accepted_counts(orc_medium *m, size_t n, const float *p, const float *d, uint32_t seed, uint32_t *out, int nthreads);
 int orc_eval_noise1d(orc_medium *m, size_t n, const float *p, const float *d, uint32_t seed, float *out4, int nthreads);
 int orc_eval(orc_medium *m, size_t n, const float *p, const float *d, const float *t, const uint32_t *pix, uint32_t sceneSeed,
              const float *info_t, const float *coeffs, float *out_val, float *out_grad, int *out_gpid, int nthreads);

@@ -91,6 +91,7 @@ SYMBOLS = {
     "scn_debug_hash4": (C.c_int, [u32p, u32p, u32p, u32p, u32p, C.c_size_t, C.c_void_p]),
     "scn_debug_pcg_stream": (C.c_int, [u32p, f32p, C.c_size_t, C.c_int, C.c_void_p]),
     "scn_debug_cell_impulses": (C.c_int, [u32p, u32p, u32p, C.c_uint32, C.c_uint32, f32p, C.c_size_t, C.c_void_p]),
+    "scn_debug_accepted_counts": (C.c_int, [MediumP, f32p, f32p, f32p, f32p, f32p, f32p, C.c_uint32, u32p, C.c_size_t, C.c_void_p]),
 }
 
 _lib = None

@@ -16,93 +16,8 @@
 
 namespace scn {
 
-static thread_local char g_err[512] = "";
-int set_error(int code, const char *fmt, ...) {
-    va_list ap; va_start(ap, fmt); vsnprintf(g_err, sizeof g_err, fmt, ap); va_end(ap);
-    return code;
-}
 static int cuda_fail(cudaError_t e, const char *what) { return set_error(SCN_ECUDA, "%s: %s", what, cudaGetErrorString(e)); }
 #define SCN_CUDA(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) return cuda_fail(e_, #x); } while (0)
-
-// ---------------------------------------------------------------- host: descriptor -> kernel parameters
-static float host_se_variance3d(const Params &p, float R, bool is_identity, float gs, float ls) { // GPF:741-754
-    double per_unit = p.density / (R * R * R);
-    double det_sqrt = 1.0;
-    if (!is_identity) { det_sqrt = p.l_aniso[0] * p.l_aniso[1] * p.l_aniso[2]; det_sqrt *= std::pow((double)gs, 3); }
-    det_sqrt *= std::pow((double)ls, 3);
-    double integral = std::pow(M_PI, 1.5) * det_sqrt;
-    return (float)(per_unit * integral);
-}
-static void field_k(const scn_field_desc &f, FieldK &k) {
-    memset(&k, 0, sizeof k);
-    k.type = f.type;
-    for (int i = 0; i < 3; ++i) k.val[i] = f.val[i];
-    const double c = 1.; // _const (never read from JSON)
-    double mn = f.min + c, mx = f.max + c, mn2 = f.min2 + c, mx2 = f.max2 + c;
-    k.la[0] = std::log(mn * mn); k.lb[0] = std::log(mx * mx); k.scale[0] = 1.0 / (f.end - f.start); k.off[0] = -f.start * k.scale[0];
-    k.la[1] = std::log(mn2 * mn2); k.lb[1] = std::log(mx2 * mx2); k.scale[1] = 1.0 / (f.end2 - f.start2); k.off[1] = -f.start2 * k.scale[1];
-}
-
-int params_from_desc(const scn_medium_desc &d, Params &p) {
-    memset(&p, 0, sizeof p);
-    if (d.correlation_context < SCN_CTX_GLOBAL || d.correlation_context > SCN_CTX_NONE)
-        return set_error(SCN_EINVAL, "correlation_context is mandatory (media/GaussianProcessMedium.cpp:104-106)");
-    if (d.use_aniso_mtx) return set_error(SCN_EUNSUPPORTED, "useAnisoMtx is not covered");
-    if (d.cov_type != SCN_COV_SQUARED_EXPONENTIAL && d.cov_type != SCN_COV_PROC_NONSTATIONARY) return set_error(SCN_EINVAL, "bad cov_type");
-    if (d.mean.type < SCN_MEAN_HOMOGENEOUS || d.mean.type > SCN_MEAN_LINEAR) return set_error(SCN_EINVAL, "bad mean type");
-    if (!(d.impulse_density >= 0.f) || d.impulse_density > 4096.f) return set_error(SCN_EINVAL, "impulse_density out of range");
-    if (d.min_step == 0) return set_error(SCN_EINVAL, "min_step must be positive");
-    p.n_imp = (uint32_t)d.impulse_density; p.density = d.impulse_density; p.global_seed = d.seed;
-    p.single_realization = d.single_realization; p.iso3d = d.isotropic_3d_sampling; p.sampling_1d = d.sampling_1d;
-    p.ctx = d.correlation_context; p.corr_xy = d.correlation_xy;
-    p.activate_conditioning = !d.single_realization && (d.correlation_context == SCN_CTX_RENEWAL || d.correlation_context == SCN_CTX_RENEWAL_PLUS);
-    p.scheme = (!d.single_realization && d.sampling_1d) ? d.sampling_scheme_1d : SCN_SCHEME_UNI;
-    p.stationary = d.cov_type == SCN_COV_SQUARED_EXPONENTIAL;
-    p.multires = !p.stationary && d.multires;
-    p.surf_vol_sep = d.surf_vol_phase_separate; p.surf_vol_thresh = d.surf_vol_phase_amp_thresh;
-    p.step_size = d.step_size; p.min_step = d.min_step; p.max_bounces = d.max_bounces;
-    { float sa = d.sigma_a * d.density, ss = d.sigma_s * d.density, st = sa + ss; p.absorption_only = ss == 0.0f; p.sigma_s_over_t = ss / st; }
-    p.sigma = d.sigma; p.kernel_scale = d.kernel_scale;
-    float l_conv = d.length_scale * std::sqrt(2.f) / 2; // GPF:658
-    for (int i = 0; i < 3; ++i) {
-        p.l_aniso[i] = l_conv * d.aniso[i];
-        float inv = 1.0f / p.l_aniso[i];
-        p.l_aniso_inv[i] = (std::isinf(inv) || std::isnan(inv)) ? 0.f : inv; // filterWithZero
-    }
-    p.l_aniso_max = std::fmax(std::fmax(p.l_aniso[0], p.l_aniso[1]), p.l_aniso[2]);
-    p.ls_max = 1.f;
-    if (!p.stationary && d.ls.type != SCN_FIELD_NONE) {
-        const scn_field_desc &f = d.ls;
-        if (f.type == SCN_FIELD_CONSTANT) p.ls_max = (float)std::fmax(std::fmax(f.val[0], f.val[1]), f.val[2]);
-        else if (f.type == SCN_FIELD_BOTTOM_TOP_LEFT_RIGHT) p.ls_max = (float)(std::fmax(f.max, f.min) * std::fmax(f.max2, f.min2));
-        else p.ls_max = (float)std::fmax(f.max, f.min);
-    }
-    field_k(d.ls, p.ls); field_k(d.var, p.var);
-    if (p.stationary) { p.ls.type = SCN_FIELD_NONE; p.var.type = SCN_FIELD_NONE; }
-    p.log_base = std::log(2.5f);
-    p.world_scale = p.stationary ? 1.f : p.ls_max;
-    p.add_seed_world = (int)std::floor(std::log(p.world_scale) / std::log(2.5f));
-    p.R_iso = d.kernel_scale;
-    {   // splattingKernelRadius(false, 1.0) (GPF:696-709, 1245-1249)
-        float ls = 1.0f;
-        if (!p.stationary) { ls *= p.multires ? 1.0 : p.ls_max; ls *= 1.f; }
-        p.R_world = d.kernel_scale * ls * p.l_aniso_max;
-    }
-    p.nf_iso = std::sqrt(host_se_variance3d(p, p.R_iso, true, 1.0f, 1.0f));
-    p.nf_world = std::sqrt(host_se_variance3d(p, p.R_world, false, p.world_scale, 1.0f));
-    { double per_unit = p.density / p.R_iso; double integral = std::sqrt(M_PI) * 1.0f; p.nf_1d = std::sqrt((float)(per_unit * integral)); }
-    for (int i = 0; i < LVL_COUNT; ++i) {
-        int k = LVL_MIN + i;
-        float s = std::pow(2.5f, (float)k); // powf, like pow(_base, level) in SCN:64-65
-        p.lvl_scale[i] = s;
-        p.lvl_add_seed[i] = (int)std::floor(std::log(s) / std::log(2.5f));
-        p.lvl_R_world[i] = d.kernel_scale * s * p.l_aniso_max;
-        p.lvl_nf_world[i] = std::sqrt(host_se_variance3d(p, p.lvl_R_world[i], false, s, 1.0f));
-    }
-    p.gp_id = d.gp_id; p.has_mean_add = d.has_mean_additional; p.id_add = d.id_additional;
-    p.mean = d.mean; p.mean_add = d.mean_additional;
-    return SCN_OK;
-}
 
 // ---------------------------------------------------------------- kernels
 constexpr int BLOCK = 128;
@@ -225,6 +140,27 @@ __global__ void k_debug_cell(const uint32_t *ci, const uint32_t *cj, const uint3
     }
 }
 
+// rejection test only, same operands as k_fast_noise3d / noise3d
+__global__ void k_debug_accept(const __grid_constant__ Params P, const float *px, const float *py, const float *pz, const float *dx, const float *dy, const float *dz,
+                               uint32_t seed, uint32_t *out, size_t n) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    f3 q = F3(px[i], py[i], pz[i]); float R = P.R_world;
+    if (P.iso3d) { Frame fr = ray_frame(P, F3(dx[i], dy[i], dz[i])); q = to_local(fr, cov_pos_w2l(P, q, 1.0f)); R = P.R_iso; }
+    f3 pg = xdiv3(q, R); f3 fl = F3(floorf(pg.x), floorf(pg.y), floorf(pg.z)); f3 frac = xsub3(pg, fl);
+    int ix = (int)fl.x, iy = (int)fl.y, iz = (int)fl.z; uint32_t cnt = 0;
+    for (int a = -1; a <= 1; ++a) for (int b = -1; b <= 1; ++b) for (int c = -1; c <= 1; ++c) {
+        Pcg g; g.seed32(xxhash32_4((uint32_t)(iz + c), (uint32_t)(iy + b), (uint32_t)(ix + a), seed));
+        float cx = xsub(frac.x, (float)a), cy = xsub(frac.y, (float)b), cz = xsub(frac.z, (float)c);
+        for (uint32_t k = 0; k < P.n_imp; ++k) {
+            float z = g.next(), y = g.next(), x = g.next(); (void)g.next();
+            float tx = xsub(cx, x), ty = xsub(cy, y), tz = xsub(cz, z);
+            if (xadd(xadd(xmul(tx, tx), xmul(ty, ty)), xmul(tz, tz)) < 1.0f) cnt++;
+        }
+    }
+    out[i] = cnt;
+}
+
 } // namespace scn
 
 // ---------------------------------------------------------------- C ABI
@@ -252,7 +188,7 @@ struct DeviceGuard {
 
 extern "C" {
 
-const char *scn_last_error(void) { return g_err; }
+const char *scn_last_error(void) { return last_error(); }
 int scn_abi_version(void) { return SCN_ABI_VERSION; }
 int scn_desc_default(scn_medium_desc *d) { return desc_default(d); }
 int scn_desc_from_json(const char *json, scn_medium_desc *d) { return desc_from_json(json, d); }
@@ -406,6 +342,16 @@ int scn_debug_cell_impulses(const uint32_t *ci, const uint32_t *cj, const uint32
     if (n == 0) return SCN_OK;
     k_debug_cell<<<grid_for(n), BLOCK, 0, (cudaStream_t)stream>>>(ci, cj, ck, seed, count, out, n);
     return check_launch("k_debug_cell");
+}
+
+int scn_debug_accepted_counts(const scn_medium *m, const float *px, const float *py, const float *pz, const float *dx, const float *dy, const float *dz,
+                              uint32_t seed, uint32_t *out, size_t n, void *stream) {
+    if (!m || !px || !py || !pz || !dx || !dy || !dz || !out) return set_error(SCN_EINVAL, "null argument");
+    if (!m->P.stationary || m->P.sampling_1d) return set_error(SCN_EUNSUPPORTED, "accepted counts: stationary 3D media only");
+    if (n == 0) return SCN_OK;
+    DeviceGuard g(m->device); if (!g.ok) return set_error(SCN_ECUDA, "cannot select device %d", m->device);
+    k_debug_accept<<<grid_for(n), BLOCK, 0, (cudaStream_t)stream>>>(m->P, px, py, pz, dx, dy, dz, seed, out, n);
+    return check_launch("k_debug_accept");
 }
 
 // ---------------------------------------------------------------- host-buffer entry points (the thin Tungsten shim calls these)

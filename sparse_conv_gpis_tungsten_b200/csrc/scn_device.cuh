@@ -729,13 +729,13 @@ SCN_FN void medium_query(const Params &P, f3 pos, f3 dir, float near_t, float fa
         double avg = ((double)grad.x + (double)grad.y + (double)grad.z) * (1.0 / 3.0);
         if (!isfinite(avg)) {
             sm.aniso = F3(1.f, 0.f, 0.f); sm.n_evals = evals; sm.weight = 0.f;
-            if (absorb) { sm.ok = true; sm.t = max_t; sm.exited = true; sm.gp_id = st.last_gp_id; st.info.t += sm.t; }
+            if (absorb) { sm.ok = true; sm.t = max_t; sm.exited = true; sm.gp_id = st.last_gp_id; st.info.t += sm.t; sm.aniso = F3(0.f, 0.f, 0.f); }
             return;
         }
     }
     sm.n_evals = evals;
     if (transmittance_only) { sm.ok = true; sm.exited = exited; sm.weight = exited ? 1.f : 0.f; return; }
-    if (absorb) { sm.ok = true; sm.t = max_t; sm.weight = exited ? 1.f : 0.f; sm.exited = true; sm.gp_id = st.last_gp_id; st.info.t += sm.t; return; }
+    if (absorb) { sm.ok = true; sm.t = max_t; sm.weight = exited ? 1.f : 0.f; sm.exited = true; sm.gp_id = st.last_gp_id; st.info.t += sm.t; sm.aniso = F3(0.f, 0.f, 0.f); return; }
     sm.exited = exited;
     if (!exited) {
         double dt = (double)grad.x * (double)dir.x + (double)grad.y * (double)dir.y + (double)grad.z * (double)dir.z;

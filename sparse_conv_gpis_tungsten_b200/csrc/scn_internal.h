@@ -10,6 +10,7 @@
 namespace scn {
 
 int set_error(int code, const char *fmt, ...);
+const char *last_error();
 int desc_default(scn_medium_desc *d);
 int desc_from_json(const char *text, scn_medium_desc *d);
 

@@ -1,0 +1,102 @@
+// scn_params.cpp — host only: error slot and scn_medium_desc -> kernel parameters.
+//
+// Everything the reference derives once per medium with the HOST libm (kernel radii, variance normalisation,
+// multi-resolution level tables whose integer seed offsets come out of logf/powf) is derived here with the same
+// libm calls, so that no integer or rejection-test operand ever depends on device libm.
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+
+#include "scn_internal.h"
+
+namespace scn {
+
+static thread_local char g_err[512] = "";
+int set_error(int code, const char *fmt, ...) {
+    va_list ap; va_start(ap, fmt); vsnprintf(g_err, sizeof g_err, fmt, ap); va_end(ap);
+    return code;
+}
+const char *last_error() { return g_err; }
+
+// ---------------------------------------------------------------- host: descriptor -> kernel parameters
+static float host_se_variance3d(const Params &p, float R, bool is_identity, float gs, float ls) { // GPF:741-754
+    double per_unit = p.density / (R * R * R);
+    double det_sqrt = 1.0;
+    if (!is_identity) { det_sqrt = p.l_aniso[0] * p.l_aniso[1] * p.l_aniso[2]; det_sqrt *= std::pow((double)gs, 3); }
+    det_sqrt *= std::pow((double)ls, 3);
+    double integral = std::pow(M_PI, 1.5) * det_sqrt;
+    return (float)(per_unit * integral);
+}
+static void field_k(const scn_field_desc &f, FieldK &k) {
+    memset(&k, 0, sizeof k);
+    k.type = f.type;
+    for (int i = 0; i < 3; ++i) k.val[i] = f.val[i];
+    const double c = 1.; // _const (never read from JSON)
+    double mn = f.min + c, mx = f.max + c, mn2 = f.min2 + c, mx2 = f.max2 + c;
+    k.la[0] = std::log(mn * mn); k.lb[0] = std::log(mx * mx); k.scale[0] = 1.0 / (f.end - f.start); k.off[0] = -f.start * k.scale[0];
+    k.la[1] = std::log(mn2 * mn2); k.lb[1] = std::log(mx2 * mx2); k.scale[1] = 1.0 / (f.end2 - f.start2); k.off[1] = -f.start2 * k.scale[1];
+}
+
+int params_from_desc(const scn_medium_desc &d, Params &p) {
+    memset(&p, 0, sizeof p);
+    if (d.correlation_context < SCN_CTX_GLOBAL || d.correlation_context > SCN_CTX_NONE)
+        return set_error(SCN_EINVAL, "correlation_context is mandatory (media/GaussianProcessMedium.cpp:104-106)");
+    if (d.use_aniso_mtx) return set_error(SCN_EUNSUPPORTED, "useAnisoMtx is not covered");
+    if (d.cov_type != SCN_COV_SQUARED_EXPONENTIAL && d.cov_type != SCN_COV_PROC_NONSTATIONARY) return set_error(SCN_EINVAL, "bad cov_type");
+    if (d.mean.type < SCN_MEAN_HOMOGENEOUS || d.mean.type > SCN_MEAN_LINEAR) return set_error(SCN_EINVAL, "bad mean type");
+    if (!(d.impulse_density >= 0.f) || d.impulse_density > 4096.f) return set_error(SCN_EINVAL, "impulse_density out of range");
+    if (d.min_step == 0) return set_error(SCN_EINVAL, "min_step must be positive");
+    p.n_imp = (uint32_t)d.impulse_density; p.density = d.impulse_density; p.global_seed = d.seed;
+    p.single_realization = d.single_realization; p.iso3d = d.isotropic_3d_sampling; p.sampling_1d = d.sampling_1d;
+    p.ctx = d.correlation_context; p.corr_xy = d.correlation_xy;
+    p.activate_conditioning = !d.single_realization && (d.correlation_context == SCN_CTX_RENEWAL || d.correlation_context == SCN_CTX_RENEWAL_PLUS);
+    p.scheme = (!d.single_realization && d.sampling_1d) ? d.sampling_scheme_1d : SCN_SCHEME_UNI;
+    p.stationary = d.cov_type == SCN_COV_SQUARED_EXPONENTIAL;
+    p.multires = !p.stationary && d.multires;
+    p.surf_vol_sep = d.surf_vol_phase_separate; p.surf_vol_thresh = d.surf_vol_phase_amp_thresh;
+    p.step_size = d.step_size; p.min_step = d.min_step; p.max_bounces = d.max_bounces;
+    { float sa = d.sigma_a * d.density, ss = d.sigma_s * d.density, st = sa + ss; p.absorption_only = ss == 0.0f; p.sigma_s_over_t = ss / st; }
+    p.sigma = d.sigma; p.kernel_scale = d.kernel_scale;
+    float l_conv = d.length_scale * std::sqrt(2.f) / 2; // GPF:658
+    for (int i = 0; i < 3; ++i) {
+        p.l_aniso[i] = l_conv * d.aniso[i];
+        float inv = 1.0f / p.l_aniso[i];
+        p.l_aniso_inv[i] = (std::isinf(inv) || std::isnan(inv)) ? 0.f : inv; // filterWithZero
+    }
+    p.l_aniso_max = std::fmax(std::fmax(p.l_aniso[0], p.l_aniso[1]), p.l_aniso[2]);
+    p.ls_max = 1.f;
+    if (!p.stationary && d.ls.type != SCN_FIELD_NONE) {
+        const scn_field_desc &f = d.ls;
+        if (f.type == SCN_FIELD_CONSTANT) p.ls_max = (float)std::fmax(std::fmax(f.val[0], f.val[1]), f.val[2]);
+        else if (f.type == SCN_FIELD_BOTTOM_TOP_LEFT_RIGHT) p.ls_max = (float)(std::fmax(f.max, f.min) * std::fmax(f.max2, f.min2));
+        else p.ls_max = (float)std::fmax(f.max, f.min);
+    }
+    field_k(d.ls, p.ls); field_k(d.var, p.var);
+    if (p.stationary) { p.ls.type = SCN_FIELD_NONE; p.var.type = SCN_FIELD_NONE; }
+    p.log_base = std::log(2.5f);
+    p.world_scale = p.stationary ? 1.f : p.ls_max;
+    p.add_seed_world = (int)std::floor(std::log(p.world_scale) / std::log(2.5f));
+    p.R_iso = d.kernel_scale;
+    {   // splattingKernelRadius(false, 1.0) (GPF:696-709, 1245-1249)
+        float ls = 1.0f;
+        if (!p.stationary) { ls *= p.multires ? 1.0 : p.ls_max; ls *= 1.f; }
+        p.R_world = d.kernel_scale * ls * p.l_aniso_max;
+    }
+    p.nf_iso = std::sqrt(host_se_variance3d(p, p.R_iso, true, 1.0f, 1.0f));
+    p.nf_world = std::sqrt(host_se_variance3d(p, p.R_world, false, p.world_scale, 1.0f));
+    { double per_unit = p.density / p.R_iso; double integral = std::sqrt(M_PI) * 1.0f; p.nf_1d = std::sqrt((float)(per_unit * integral)); }
+    for (int i = 0; i < LVL_COUNT; ++i) {
+        int k = LVL_MIN + i;
+        float s = std::pow(2.5f, (float)k); // powf, like pow(_base, level) in SCN:64-65
+        p.lvl_scale[i] = s;
+        p.lvl_add_seed[i] = (int)std::floor(std::log(s) / std::log(2.5f));
+        p.lvl_R_world[i] = d.kernel_scale * s * p.l_aniso_max;
+        p.lvl_nf_world[i] = std::sqrt(host_se_variance3d(p, p.lvl_R_world[i], false, s, 1.0f));
+    }
+    p.gp_id = d.gp_id; p.has_mean_add = d.has_mean_additional; p.id_add = d.id_additional;
+    p.mean = d.mean; p.mean_add = d.mean_additional;
+    return SCN_OK;
+}
+
+} // namespace scn

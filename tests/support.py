@@ -1,0 +1,408 @@
+"""Shared test infrastructure: media configurations, seeded inputs, and one driver class over the three CPU-side
+implementations that share the array-of-structs harness signatures:
+
+  ref  oracle/_ref/libscn_ref.so        the UNMODIFIED reference compiled from /root/reference (container only)
+  orc  oracle/_build/libscn_oracle.so   the plain-C restatement (the oracle; always buildable)
+  sim  tests/hostsim/_build/...         the product's device header compiled for the host (logic check, CPU CI leg)
+
+Only tests/, bench.py's cpu_baseline/reference legs and __graft_entry__.smoke() import this module.
+"""
+import copy
+import ctypes as C
+import json
+import os
+import subprocess
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ORACLE_DIR = os.path.join(ROOT, "oracle")
+REF_LIB = os.path.join(ORACLE_DIR, "_ref", "libscn_ref.so")
+ORC_LIB = os.path.join(ORACLE_DIR, "_build", "libscn_oracle.so")
+SIM_DIR = os.path.join(ROOT, "tests", "hostsim")
+SIM_LIB = os.path.join(SIM_DIR, "_build", "libscn_hostsim.so")
+GOLDEN_DIR = os.path.join(ROOT, "tests", "golden")
+
+import sys
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+# ------------------------------------------------------------------------------------------------ media
+_BASE = {
+    "name": "gpis", "type": "sparse_conv_noise", "sigma_a": 0.0, "sigma_s": 1.0, "density": 1.0,
+    "correlation_context": "none", "single_realization": True, "step_size": 0.01, "impulse_density": 3,
+    "isotropic_3D_sampling": True, "1D_sampling": False, "seed": 1,
+    "phase_function": {"type": "brdf", "bsdf": {"type": "lambert", "albedo": 0.8}},
+    "gaussian_process": {"type": "standard", "mean": {"type": "spherical", "center": [0, 0, 0], "radius": 1.0},
+                         "covariance": {"type": "squared_exponential", "sigma": 0.05, "lengthScale": 0.1, "aniso": [1, 1, 1]}},
+}
+_NONSTAT = {"type": "proc_nonstationary", "multiResolutionGrid": True,
+            "cov": {"type": "squared_exponential", "sigma": 0.05, "lengthScale": 0.1, "aniso": [1, 1, 1]},
+            "ls": {"type": "noise", "noise": "bottom_top", "min": 0.5, "max": 3.0, "start": -1.0, "end": 1.0}}
+
+
+def medium(**kw):
+    m = copy.deepcopy(_BASE)
+    cov = kw.pop("covariance", None)
+    mean = kw.pop("mean", None)
+    m.update(kw)
+    if cov is not None:
+        m["gaussian_process"]["covariance"] = copy.deepcopy(cov)
+    if mean is not None:
+        m["gaussian_process"]["mean"] = copy.deepcopy(mean)
+    return m
+
+
+def microbench_medium(density=3, iso=True, one_d=False):
+    """BASELINE.json configs[1] / SURVEY §8(d) C2: stationary SE sigma=1 l=1 aniso=1 localScale=3, single realization, seed 1."""
+    return medium(impulse_density=density, isotropic_3D_sampling=iso, **{"1D_sampling": one_d},
+                  covariance={"type": "squared_exponential", "sigma": 1, "lengthScale": 1, "aniso": [1, 1, 1], "localScale": 3})
+
+
+def _nonstat(multires=True, **kw):
+    c = copy.deepcopy(_NONSTAT)
+    c["multiResolutionGrid"] = multires
+    c.update(kw)
+    return c
+
+
+MEDIA = {
+    # BASELINE.json configs
+    "c1_sphere_3d_none": medium(),
+    "c2_micro_iso": microbench_medium(3, True),
+    "c2_micro_world": microbench_medium(3, False),
+    "c3_1d_renewal": medium(correlation_context="renewal", single_realization=False, **{"1D_sampling": True, "1D_sampling_scheme": "uni"}),
+    "c4_1d_renewalplus_xy_mis": medium(correlation_context="renewal+", single_realization=False,
+                                        **{"1D_sampling": True, "1D_sampling_scheme": "mis", "1D_gradient_correlationXY": True}),
+    "c5_multires_nonstat_renewalplus": medium(correlation_context="renewal+", single_realization=False, covariance=_nonstat(True)),
+    # variants covering the remaining branches
+    "world_3d_none": medium(isotropic_3D_sampling=False),
+    "world_3d_renewalplus": medium(isotropic_3D_sampling=False, correlation_context="renewal+", single_realization=False),
+    "iso_3d_renewal": medium(correlation_context="renewal", single_realization=False),
+    "iso_3d_renewalplus_aniso": medium(correlation_context="renewal+", single_realization=False,
+                                       covariance={"type": "squared_exponential", "sigma": 0.07, "lengthScale": 0.12, "aniso": [1, 0.5, 2], "localScale": 2.5}),
+    "iso_3d_global": medium(correlation_context="global", single_realization=False),
+    "1d_renewalplus_noxy": medium(correlation_context="renewal+", single_realization=False, **{"1D_sampling": True, "1D_sampling_scheme": "nee"}),
+    "1d_none_single": medium(**{"1D_sampling": True}),
+    "linear_mean_world": medium(isotropic_3D_sampling=False, impulse_density=5,
+                                mean={"type": "linear", "reference_point": [0, -0.2, 0], "direction": [0.2, 1, 0.1], "scale": 0.8, "min": -0.5}),
+    "homogeneous_mean_density8": medium(impulse_density=8.7, mean={"type": "homogeneous", "offset": 0.01}),
+    "nonstat_bruteforce_iso": medium(correlation_context="renewal+", single_realization=False, covariance=_nonstat(False)),
+    "nonstat_bruteforce_world_var": medium(isotropic_3D_sampling=False, correlation_context="renewal", single_realization=False,
+                                           covariance=_nonstat(False, var={"type": "noise", "noise": "left_right", "min": 0.5, "max": 2.0, "start": -1.5, "end": 1.5})),
+    "multires_world": medium(isotropic_3D_sampling=False, correlation_context="renewal+", single_realization=False, covariance=_nonstat(True)),
+    "multires_1d_xy": medium(correlation_context="renewal+", single_realization=False, covariance=_nonstat(True),
+                             **{"1D_sampling": True, "1D_sampling_scheme": "mis", "1D_gradient_correlationXY": True}),
+    "multires_1d_renewal": medium(correlation_context="renewal", single_realization=False, covariance=_nonstat(True, ls={"type": "noise", "noise": "bottom_top_left_right", "min": 0.4, "max": 1.5, "start": -1, "end": 1, "min2": 0.8, "max2": 1.6, "start2": -1.2, "end2": 1.1}),
+                                  **{"1D_sampling": True}),
+    "csg_two_spheres": medium(**{"gaussian_process": {"type": "csg",
+                                 "left": {"type": "standard", "id": 0, "mean": {"type": "spherical", "center": [-0.4, 0, 0], "radius": 0.7},
+                                          "covariance": {"type": "squared_exponential", "sigma": 0.05, "lengthScale": 0.1, "aniso": [1, 1, 1]}},
+                                 "right": {"type": "standard", "id": 1, "mean": {"type": "spherical", "center": [0.5, 0.1, 0], "radius": 0.6},
+                                           "covariance": {"type": "squared_exponential", "sigma": 0.05, "lengthScale": 0.1, "aniso": [1, 1, 1]}}}}),
+    "absorption_only": medium(sigma_a=1.0, sigma_s=0.0),
+}
+IS_1D = {k: bool(v.get("1D_sampling")) for k, v in MEDIA.items()}
+
+
+# ------------------------------------------------------------------------------------------------ seeded inputs
+def eval_points(n, seed=1234, lo=-8.0, hi=8.0):
+    """points uniform in [-8,8]^3 (seed 1234) and unit directions (seed 1235)."""
+    p = np.random.default_rng(seed).uniform(lo, hi, (n, 3)).astype(np.float32)
+    d = np.random.default_rng(seed + 1).normal(size=(n, 3))
+    d = (d / np.linalg.norm(d, axis=1, keepdims=True)).astype(np.float32)
+    return np.ascontiguousarray(p), np.ascontiguousarray(d)
+
+
+def camera_rays(n, seed=7, half=1.5, secondary=False):
+    """Rays through the 3-unit cube of Appendix A.1: pinhole at (0,0,5) looking at the origin (primary), or rays
+    started inside the cube in random directions with a previous value/gradient to condition on (secondary)."""
+    rng = np.random.default_rng(seed)
+    if not secondary:
+        o = np.tile(np.array([0, 0, 5], np.float32), (n, 1))
+        tgt = rng.uniform(-1.3, 1.3, (n, 3)); tgt[:, 2] = 0
+        d = tgt - o
+    else:
+        o = rng.uniform(-1.2, 1.2, (n, 3)).astype(np.float32)
+        d = rng.normal(size=(n, 3))
+    d = (d / np.linalg.norm(d, axis=1, keepdims=True)).astype(np.float32)
+    # slab intersection with [-half, half]^3
+    with np.errstate(divide="ignore", invalid="ignore"):
+        t0 = (-half - o) / d; t1 = (half - o) / d
+    tn = np.minimum(t0, t1).max(axis=1); tf = np.maximum(t0, t1).min(axis=1)
+    tn = np.maximum(tn, 0).astype(np.float32); tf = tf.astype(np.float32)
+    miss = tf <= tn
+    tf[miss] = tn[miss] + 0.5
+    if secondary:
+        tn[:] = 0.0
+    rays = {"o": np.ascontiguousarray(o.astype(np.float32)), "d": np.ascontiguousarray(d), "tmin": tn, "tmax": tf,
+            "u": rng.uniform(0, 1, n).astype(np.float32),
+            "pix": np.ascontiguousarray(np.stack([rng.integers(0, 512, n), rng.integers(0, 512, n), rng.integers(0, 64, n),
+                                                   rng.integers(0, 6, n) if secondary else np.zeros(n, np.int64)], 1).astype(np.uint32))}
+    st = {"first_scatter": np.ones(n, np.uint8), "last_val": np.zeros(n, np.float32), "last_grad": np.zeros((n, 3), np.float64),
+          "bounce": np.zeros(n, np.int32), "last_gp_id": np.zeros(n, np.int32), "info_t": np.zeros(n, np.float32)}
+    if secondary:
+        st["first_scatter"][:] = 0
+        st["last_val"] = rng.normal(0, 0.02, n).astype(np.float32)
+        g = rng.normal(size=(n, 3)); g /= np.linalg.norm(g, axis=1, keepdims=True)
+        st["last_grad"] = np.ascontiguousarray((g * rng.uniform(0.5, 1.5, (n, 1))).astype(np.float32).astype(np.float64))
+        st["bounce"] = rng.integers(1, 5, n).astype(np.int32)
+        st["info_t"] = rng.uniform(0, 3, n).astype(np.float32)
+    return rays, st
+
+
+# ------------------------------------------------------------------------------------------------ library drivers
+def _vp(a):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+def build_oracle():
+    subprocess.run(["make", "-s", "-C", ORACLE_DIR, "oracle"], check=True)
+    return ORC_LIB
+
+
+def build_hostsim():
+    src = os.path.join(SIM_DIR, "hostsim.cpp")
+    csrc = os.path.join(ROOT, "sparse_conv_gpis_tungsten_b200", "csrc")
+    deps = [src, os.path.join(csrc, "scn_device.cuh"), os.path.join(csrc, "scn_params.cpp"), os.path.join(csrc, "scn_internal.h")]
+    if os.path.exists(SIM_LIB) and all(os.path.getmtime(SIM_LIB) >= os.path.getmtime(d) for d in deps):
+        return SIM_LIB
+    os.makedirs(os.path.dirname(SIM_LIB), exist_ok=True)
+    subprocess.run(["g++", "-std=c++17", "-O2", "-msse4.2", "-ffp-contract=off", "-fPIC", "-shared", "-o", SIM_LIB, src,
+                    os.path.join(csrc, "scn_params.cpp")], check=True)
+    return SIM_LIB
+
+
+def desc_from_json(mj):
+    from sparse_conv_gpis_tungsten_b200.medium import SparseConvolutionNoiseMedium
+    return SparseConvolutionNoiseMedium.desc_from_json(mj)
+
+
+class CpuImpl:
+    """ref / orc / sim behind one interface (array-of-structs, numpy in, numpy out)."""
+
+    def __init__(self, kind, medium_json, threads=None):
+        self.kind = kind
+        self.threads = threads or min(8, os.cpu_count() or 1)
+        self.mj = medium_json
+        js = json.dumps(medium_json).encode()
+        if kind == "ref":
+            if not os.path.exists(REF_LIB):
+                raise FileNotFoundError(REF_LIB)
+            self.lib = C.CDLL(REF_LIB)
+            self.pre = "ref_"
+            self.lib.ref_medium_create.restype = C.c_void_p
+            self.lib.ref_last_error.restype = C.c_char_p
+            self.h = self.lib.ref_medium_create(js)
+            if not self.h:
+                raise RuntimeError("reference refused the medium: %s" % self.lib.ref_last_error().decode())
+        else:
+            self.lib = C.CDLL(build_oracle() if kind == "orc" else build_hostsim())
+            self.pre = "orc_" if kind == "orc" else "sim_"
+            create = getattr(self.lib, self.pre + "medium_create")
+            create.restype = C.c_void_p
+            self.desc = desc_from_json(js)
+            self.h = create(C.byref(self.desc))
+            if not self.h:
+                raise RuntimeError("%s refused the medium" % kind)
+        self.hp = C.c_void_p(self.h)
+
+    def close(self):
+        if self.h:
+            getattr(self.lib, self.pre + "medium_destroy")(self.hp)
+            self.h = None
+
+    def fn(self, name):
+        return getattr(self.lib, self.pre + name)
+
+    def eval_noise(self, p, d, seed):
+        n = len(p)
+        out = np.zeros((n, 4), np.float32)
+        one_d = bool(self.mj.get("1D_sampling"))
+        if one_d and self.kind == "ref":
+            raise NotImplementedError("the reference harness has no 1D noise-level entry; use eval()")
+        name = "eval_noise1d" if (one_d and self.kind == "orc") else "eval_noise3d"
+        self.fn(name)(self.hp, C.c_size_t(n), _vp(p), _vp(d), C.c_uint32(seed), _vp(out), self.threads)
+        return out
+
+    def eval(self, p, d, t=None, pix=None, scene_seed=0, info_t=None, coeffs=None, value=True, gradient=True):
+        n = len(p)
+        if pix is None:
+            pix = np.zeros((n, 4), np.uint32)
+        val = np.zeros(n, np.float32) if value else None
+        grad = np.zeros((n, 3), np.float32) if gradient else None
+        gpid = np.zeros(n, np.int32) if value else None
+        self.fn("eval")(self.hp, C.c_size_t(n), _vp(p), _vp(d), _vp(t), _vp(pix), C.c_uint32(scene_seed), _vp(info_t), _vp(coeffs),
+                        _vp(val), _vp(grad), _vp(gpid), self.threads)
+        return {"val": val, "grad": grad, "gp_id": gpid}
+
+    def conditioning(self, p, d, target_val, target_grad, pix, scene_seed=0, info_t=None):
+        n = len(p)
+        out = np.zeros((n, 7), np.float32)
+        self.fn("conditioning")(self.hp, C.c_size_t(n), _vp(p), _vp(d), _vp(target_val), _vp(target_grad), _vp(pix), C.c_uint32(scene_seed),
+                                _vp(info_t), _vp(out), self.threads)
+        return out
+
+    def sample_distance(self, rays, state, scene_seed=0):
+        n = len(rays["u"])
+        st = {k: np.array(v, copy=True) for k, v in state.items()}
+        out = {"ok": np.zeros(n, np.uint8), "exited": np.zeros(n, np.uint8), "t": np.zeros(n, np.float32), "cont_t": np.zeros(n, np.float32),
+               "grad": np.zeros((n, 3), np.float64), "gp_id": np.zeros(n, np.int32), "scheme": np.zeros(n, np.uint8),
+               "coeffs": np.zeros((n, 7), np.float32), "weight": np.zeros((n, 3), np.float32)}
+        self.fn("sample_distance")(self.hp, C.c_size_t(n), _vp(rays["o"]), _vp(rays["d"]), _vp(rays["tmin"]), _vp(rays["tmax"]), _vp(rays["u"]),
+                                   _vp(rays["pix"]), C.c_uint32(scene_seed),
+                                   _vp(st["first_scatter"]), _vp(st["last_val"]), _vp(st["last_grad"]), _vp(st["bounce"]), _vp(st["last_gp_id"]), _vp(st["info_t"]),
+                                   _vp(out["ok"]), _vp(out["exited"]), _vp(out["t"]), _vp(out["cont_t"]), _vp(out["grad"]), _vp(out["gp_id"]), _vp(out["scheme"]),
+                                   _vp(out["coeffs"]), _vp(out["weight"]), self.threads)
+        out["state"] = st
+        return out
+
+    def transmittance(self, rays, state, scene_seed=0):
+        n = len(rays["u"])
+        T = np.zeros(n, np.float32)
+        self.fn("transmittance")(self.hp, C.c_size_t(n), _vp(rays["o"]), _vp(rays["d"]), _vp(rays["tmin"]), _vp(rays["tmax"]), _vp(rays["u"]),
+                                 _vp(rays["pix"]), C.c_uint32(scene_seed),
+                                 _vp(state["first_scatter"]), _vp(state["last_val"]), _vp(state["last_grad"]), _vp(state["bounce"]), _vp(state["last_gp_id"]),
+                                 _vp(state["info_t"]), _vp(T), self.threads)
+        return T
+
+    def nee(self, d, normal, p, t_segment, pix, scene_seed=0, info_t=None, coeffs=None):
+        n = len(p)
+        pdf = np.zeros(n, np.float32); grad = np.zeros((n, 3), np.float32)
+        self.fn("nee")(self.hp, C.c_size_t(n), _vp(d), _vp(normal), _vp(p), _vp(t_segment), _vp(pix), C.c_uint32(scene_seed), _vp(info_t), _vp(coeffs),
+                       _vp(pdf), _vp(grad), self.threads)
+        return pdf, grad
+
+    def eval_count(self):
+        if self.kind != "orc":
+            return None
+        f = self.lib.orc_last_eval_count
+        f.restype = C.c_uint64
+        return int(f())
+
+
+def have_ref():
+    return os.path.exists(REF_LIB)
+
+
+# ------------------------------------------------------------------------------------------------ comparisons
+def rel_err(a, b, floor=None):
+    """|a-b| / max(|b|, floor); floor defaults to the rms of b (a value near a zero of the field has no relative scale)."""
+    a = np.asarray(a, np.float64); b = np.asarray(b, np.float64)
+    if floor is None:
+        floor = float(np.sqrt(np.mean(b * b))) if b.size else 1.0
+        floor = floor if floor > 0 else 1.0
+    return np.abs(a - b) / np.maximum(np.abs(b), floor)
+
+
+def compare_queries(a, b, tol=1e-4):
+    """Parity report for two sampleDistance result sets (SURVEY H-sign): decision mismatches are counted separately
+    from the 1e-4 tolerance on matched queries."""
+    same = (a["ok"] == b["ok"]) & (a["exited"] == b["exited"])
+    same &= np.abs(a["t"].astype(np.float64) - b["t"]) <= 1e-3 * np.maximum(1.0, np.abs(b["t"]))  # same march step
+    rep = {"n": len(same), "decision_mismatch": int((~same).sum())}
+    m = same & (a["ok"] != 0)
+    rep["t_rel"] = float(rel_err(a["t"][m], b["t"][m], 1e-3).max()) if m.any() else 0.0
+    g_floor = float(np.sqrt(np.mean(np.asarray(b["grad"][m], np.float64) ** 2))) if m.any() else 1.0
+    rep["grad_rel"] = float(rel_err(a["grad"][m], b["grad"][m], max(g_floor, 1e-12)).max()) if m.any() else 0.0
+    rep["ok_fraction"] = float((b["ok"] != 0).mean())
+    rep["hit_fraction"] = float(((b["ok"] != 0) & (b["exited"] == 0)).mean())
+    return rep
+
+
+# ------------------------------------------------------------------------------------------------ the product on the GPU
+class GpuImpl:
+    """The CUDA library behind the same interface as CpuImpl (array-of-structs numpy in/out), through the package's
+    host mirror and the C ABI.  `host=True` routes through the *_host entry points (numpy buffers)."""
+
+    def __init__(self, medium_json, device=0, host=False):
+        import torch
+        from sparse_conv_gpis_tungsten_b200 import SparseConvolutionNoiseMedium
+        self.torch = torch
+        self.m = SparseConvolutionNoiseMedium.from_json(medium_json, device)
+        self.dev = torch.device("cuda", device)
+        self.host = host
+        self.mj = medium_json
+
+    def close(self):
+        self.m.close()
+
+    def _f(self, a):  # (n,k) numpy -> list of k contiguous 1-D buffers
+        a = np.asarray(a)
+        cols = [np.ascontiguousarray(a[:, j]) for j in range(a.shape[1])] if a.ndim == 2 else [np.ascontiguousarray(a)]
+        if self.host:
+            return cols
+        out = []
+        for c in cols:
+            if c.dtype == np.uint32:
+                c = c.view(np.int32)
+            if c.dtype == np.float64:
+                c = c.astype(np.float32)
+            out.append(self.torch.from_numpy(c).to(self.dev))
+        return out
+
+    def _np(self, t):
+        if isinstance(t, np.ndarray):
+            return t
+        return t.detach().cpu().numpy()
+
+    def eval_noise(self, p, d, seed):
+        outs = self.m.eval_noise(self._f(p), self._f(d), seed)
+        return np.stack([self._np(o) for o in outs], 1)
+
+    def eval(self, p, d, t=None, pix=None, scene_seed=0, info_t=None, coeffs=None, value=True, gradient=True):
+        r = self.m.evaluate(self._f(p), self._f(d), t=None if t is None else self._f(t)[0], info_t=None if info_t is None else self._f(info_t)[0],
+                            pix=None if pix is None else self._f(pix), scene_seed=scene_seed, ctx=None if coeffs is None else self._f(coeffs),
+                            value=value, gradient=gradient)
+        out = {"val": None, "grad": None, "gp_id": None}
+        if value:
+            out["val"] = self._np(r["val"]); out["gp_id"] = self._np(r["gp_id"])
+        if gradient:
+            out["grad"] = np.stack([self._np(r[k]) for k in ("gx", "gy", "gz")], 1)
+        return out
+
+    def conditioning(self, p, d, target_val, target_grad, pix, scene_seed=0, info_t=None):
+        assert not self.host
+        outs = self.m.conditioning(self._f(p), self._f(d), self._f(target_val)[0], self._f(target_grad), info_t=None if info_t is None else self._f(info_t)[0],
+                                   pix=self._f(pix), scene_seed=scene_seed)
+        return np.stack([self._np(o) for o in outs], 1)
+
+    def _rays_state(self, rays, state):
+        from sparse_conv_gpis_tungsten_b200 import medium as M
+        r = dict(zip(("ox", "oy", "oz"), self._f(rays["o"]))); r.update(zip(("dx", "dy", "dz"), self._f(rays["d"])))
+        for k in ("tmin", "tmax", "u"):
+            r[k] = self._f(rays[k])[0]
+        r.update(zip(("px", "py", "spp", "segment"), self._f(rays["pix"])))
+        s = {"first_scatter": self._f(state["first_scatter"])[0], "last_val": self._f(state["last_val"])[0], "bounce": self._f(state["bounce"])[0],
+             "last_gp_id": self._f(state["last_gp_id"])[0], "info_t": self._f(state["info_t"])[0]}
+        lg = np.asarray(state["last_grad"], np.float32)
+        s.update(zip(("last_gx", "last_gy", "last_gz"), self._f(lg)))
+        n = len(rays["u"])
+        s["scheme"] = self._f(np.zeros(n, np.uint8))[0]
+        for k in M.CTX_NAMES:
+            s[k] = self._f(np.zeros(n, np.float32))[0]
+        return r, s
+
+    def sample_distance(self, rays, state, scene_seed=0):
+        from sparse_conv_gpis_tungsten_b200 import medium as M
+        r, s = self._rays_state(rays, state)
+        o = self.m.sample_distance(r, s, scene_seed=scene_seed, count_evals=True)
+        out = {"ok": self._np(o["ok"]), "exited": self._np(o["exited"]), "t": self._np(o["t"]), "cont_t": self._np(o["continued_t"]),
+               "grad": np.stack([self._np(o[k]) for k in ("gx", "gy", "gz")], 1).astype(np.float64), "gp_id": self._np(o["gp_id"]),
+               "scheme": self._np(o["scheme"]), "coeffs": np.stack([self._np(s[k]) for k in M.CTX_NAMES], 1),
+               "weight": np.repeat(self._np(o["weight"])[:, None], 3, 1), "n_evals": self._np(o["n_evals"]).view(np.uint32)}
+        out["state"] = {"first_scatter": self._np(s["first_scatter"]), "last_val": self._np(s["last_val"]),
+                        "last_grad": np.stack([self._np(s[k]) for k in ("last_gx", "last_gy", "last_gz")], 1).astype(np.float64),
+                        "bounce": self._np(s["bounce"]), "last_gp_id": self._np(s["last_gp_id"]), "info_t": self._np(s["info_t"])}
+        return out
+
+    def transmittance(self, rays, state, scene_seed=0):
+        r, s = self._rays_state(rays, state)
+        return self._np(self.m.transmittance(r, s, scene_seed=scene_seed))
+
+    def nee(self, d, normal, p, t_segment, pix, scene_seed=0, info_t=None, coeffs=None):
+        assert not self.host
+        kw = dict(info_t=None if info_t is None else self._f(info_t)[0], pix=self._f(pix), scene_seed=scene_seed, ctx=None if coeffs is None else self._f(coeffs))
+        pdf = self.m.nee_pdf(self._f(d), self._f(normal), self._f(p), self._f(t_segment)[0], **kw)
+        g = self.m.nee_grad(self._f(d), self._f(normal), self._f(p), **kw)
+        return self._np(pdf), np.stack([self._np(x) for x in g], 1)

@@ -1,0 +1,185 @@
+"""GPU leg (`pytest -m gpu`, B200): the CUDA kernels, called through the C ABI, against (1) the golden vectors recorded
+from the unmodified reference, (2) the oracle on fresh seeded inputs, (3) size-independent properties at BASELINE.json's
+full microbench size.  Integer work (hash, PCG, impulse positions, accepted-impulse counts) must be bit-exact;
+floating-point results within 1e-4 relative (north_star), with decision flips of the march counted separately."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+import golden_util as G
+import support as S
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-4
+
+
+@pytest.fixture(scope="module")
+def torch_cuda():
+    import torch
+    assert torch.cuda.is_available(), "GPU tests need a CUDA device"
+    return torch
+
+
+def _dev(torch, a):
+    a = np.ascontiguousarray(a)
+    if a.dtype == np.uint32:
+        a = a.view(np.int32)
+    return torch.from_numpy(a).cuda()
+
+
+def test_hash_pcg_impulses_bit_exact(torch_cuda, built_library):
+    torch = torch_cuda
+    lib = built_library
+    from sparse_conv_gpis_tungsten_b200 import abi
+    g = dict(np.load(S.GOLDEN_DIR + "/primitives.npz"))
+    keys = g["keys"]
+    cols = [_dev(torch, keys[:, j]) for j in range(4)]
+    out = torch.zeros(len(keys), dtype=torch.int32, device="cuda")
+    p = lambda t, ct: C.cast(C.c_void_p(t.data_ptr()), ct)
+    abi.check(lib.scn_debug_hash4(*[p(c, abi.u32p) for c in cols], p(out, abi.u32p), len(keys), None))
+    assert np.array_equal(out.cpu().numpy().view(np.uint32), g["h4"])
+    seeds = _dev(torch, g["seeds"])
+    st = torch.zeros(len(g["seeds"]) * 16, dtype=torch.float32, device="cuda")
+    abi.check(lib.scn_debug_pcg_stream(p(seeds, abi.u32p), p(st, abi.f32p), len(g["seeds"]), 16, None))
+    assert np.array_equal(st.cpu().numpy().reshape(-1, 16), g["streams"])  # set_state(seed) then 16 draws
+    # per-cell impulses against the oracle, including negative (wrapped) cell indices
+    orc = C.CDLL(S.build_oracle())
+    rng = np.random.default_rng(9)
+    cells = rng.integers(-50, 50, (512, 3)).astype(np.int32).view(np.uint32)
+    count = 9
+    got = torch.zeros(512 * count * 4, dtype=torch.float32, device="cuda")
+    cc = [_dev(torch, cells[:, j]) for j in range(3)]
+    abi.check(lib.scn_debug_cell_impulses(p(cc[0], abi.u32p), p(cc[1], abi.u32p), p(cc[2], abi.u32p), 12345, count, p(got, abi.f32p), 512, None))
+    want = np.zeros((512, count * 4), np.float32)
+    for i, c in enumerate(cells):
+        orc.orc_cell_impulses(C.c_uint32(int(c[0])), C.c_uint32(int(c[1])), C.c_uint32(int(c[2])), C.c_uint32(12345), C.c_uint32(count), want[i].ctypes.data_as(C.c_void_p))
+    assert np.array_equal(got.cpu().numpy().reshape(512, -1), want)
+
+
+@pytest.mark.parametrize("name", sorted(S.MEDIA))
+def test_kernels_vs_reference_golden(torch_cuda, name):
+    impl = S.GpuImpl(S.MEDIA[name])
+    G.check_against_golden(impl, name, G.load(name), exact=False, allow_mismatch=1)
+    impl.close()
+
+
+@pytest.mark.parametrize("name", ["c1_sphere_3d_none", "c3_1d_renewal"])
+def test_host_buffer_entry_points(torch_cuda, name):
+    """The *_host entry points (numpy in/out, staged through the medium's arena) give the same answers."""
+    g = G.load(name)
+    dev, host = S.GpuImpl(S.MEDIA[name]), S.GpuImpl(S.MEDIA[name], host=True)
+    e1 = dev.eval(g["p"], g["d"], g["tt"], g["pix"], 77, g["info_t"], g["coeffs"]); e2 = host.eval(g["p"], g["d"], g["tt"], g["pix"], 77, g["info_t"], g["coeffs"])
+    assert np.array_equal(e1["val"], e2["val"]) and np.array_equal(e1["grad"], e2["grad"])
+    for tag in ("pri", "sec"):
+        rays, st, _ = G.rays_state(g, tag)
+        a, b = dev.sample_distance(rays, st, 99), host.sample_distance(rays, st, 99)
+        for k in ("ok", "exited", "t", "grad", "coeffs", "n_evals"):
+            assert np.array_equal(a[k], b[k]), k
+        for k in a["state"]:
+            assert np.array_equal(a["state"][k], b["state"][k]), k
+        assert np.array_equal(dev.transmittance(rays, st, 99), host.transmittance(rays, st, 99))
+
+
+@pytest.mark.parametrize("iso", [True, False])
+@pytest.mark.parametrize("density", [1, 2, 4, 8, 16, 32, 64])
+def test_microbench_noise_vs_oracle(torch_cuda, iso, density):
+    """BASELINE.json configs[1]: value + gradient of the 3D noise, impulse_density sweep, isotropic vs world space."""
+    n = 16384 if density <= 8 else 4096
+    mj = S.microbench_medium(density, iso)
+    p, d = S.eval_points(n)
+    gpu, orc = S.GpuImpl(mj), S.CpuImpl("orc", mj)
+    a, b = gpu.eval_noise(p, d, 1), orc.eval_noise(p, d, 1)
+    assert S.rel_err(a, b).max() <= TOL
+    # accepted-impulse sets: counts must agree exactly (target 0 differing evals)
+    torch = torch_cuda
+    from sparse_conv_gpis_tungsten_b200 import abi
+    cols = [_dev(torch, p[:, j]) for j in range(3)] + [_dev(torch, d[:, j]) for j in range(3)]
+    cnt = torch.zeros(n, dtype=torch.int32, device="cuda")
+    pp = lambda t, ct: C.cast(C.c_void_p(t.data_ptr()), ct)
+    abi.check(abi.load().scn_debug_accepted_counts(gpu.m._h, *[pp(c, abi.f32p) for c in cols], 1, pp(cnt, abi.u32p), n, None))
+    want = np.zeros(n, np.uint32)
+    orc.lib.orc_accepted_counts(orc.hp, C.c_size_t(n), p.ctypes.data_as(C.c_void_p), d.ctypes.data_as(C.c_void_p), C.c_uint32(1), want.ctypes.data_as(C.c_void_p), 8)
+    assert np.array_equal(cnt.cpu().numpy().view(np.uint32), want)
+    assert abs(want.mean() / (27 * density) - 4 * np.pi / 81) < 0.01  # a = 4*pi/81 of the impulses are inside
+
+
+def test_microbench_full_size_properties(torch_cuda):
+    """2^26 points (the size BASELINE.json quotes): determinism, agreement with the oracle on a strided subsample,
+    unit variance (the reference normalises by sqrt(variance3D)), gradient consistent with central differences."""
+    torch = torch_cuda
+    from sparse_conv_gpis_tungsten_b200 import SparseConvolutionNoiseMedium
+    n = 1 << 26
+    mj = S.microbench_medium(3, True)
+    m = SparseConvolutionNoiseMedium.from_json(mj)
+    gen = torch.Generator(device="cuda"); gen.manual_seed(1234)
+    P = [(torch.rand(n, generator=gen, device="cuda") * 16 - 8) for _ in range(3)]
+    gen.manual_seed(1235)
+    D = torch.randn(3, n, generator=gen, device="cuda"); D = D / D.norm(dim=0, keepdim=True); D = [D[0].contiguous(), D[1].contiguous(), D[2].contiguous()]
+    o1 = m.eval_noise(P, D, 1); o2 = m.eval_noise(P, D, 1)
+    for a, b in zip(o1, o2):
+        assert torch.equal(a, b)
+    assert bool(torch.isfinite(o1[0]).all())
+    var = float(o1[0].double().var())
+    assert abs(var - 1.0) < 0.02, var
+    assert abs(float(o1[0].double().mean())) < 1e-3
+    idx = torch.arange(0, n, n // 2048, device="cuda")
+    p = torch.stack([x[idx] for x in P], 1).cpu().numpy(); d = torch.stack([x[idx] for x in D], 1).cpu().numpy()
+    orc = S.CpuImpl("orc", mj)
+    want = orc.eval_noise(np.ascontiguousarray(p), np.ascontiguousarray(d), 1)
+    got = torch.stack([x[idx] for x in o1], 1).cpu().numpy()
+    assert S.rel_err(got, want).max() <= TOL
+    # gradient vs central differences of the value along x (same ray direction => same rotated lattice)
+    h = 1e-3
+    sub = [x[:4096].contiguous() for x in P]; dsub = [x[:4096].contiguous() for x in D]
+    vp = m.eval_noise([sub[0] + h, sub[1], sub[2]], dsub, 1)[0]; vm = m.eval_noise([sub[0] - h, sub[1], sub[2]], dsub, 1)[0]
+    fd = (vp - vm) / (2 * h)
+    gx = m.eval_noise(sub, dsub, 1)[1]
+    ok = (fd - gx).abs() < 2e-2 * (1 + gx.abs())
+    assert float(ok.float().mean()) > 0.98  # the kernel is truncated at its radius: a few points straddle a cut-off
+
+
+def test_march_round_trip_properties(torch_cuda):
+    """Size-independent properties of the query kernels on 2^18 rays: every reported hit brackets a sign change of the
+    field (evaluateValue at t is on sign0's side, one step later is not), transmittance is 1 exactly where
+    sampleDistance exits, and a replayed wavefront is bit-identical."""
+    n = 1 << 18
+    mj = S.MEDIA["c1_sphere_3d_none"]
+    rays, st = S.camera_rays(n, seed=3)
+    gpu = S.GpuImpl(mj)
+    a = gpu.sample_distance(rays, st, 5); b = gpu.sample_distance(rays, st, 5)
+    for k in ("ok", "exited", "t", "grad"):
+        assert np.array_equal(a[k], b[k])
+    T = gpu.transmittance(rays, st, 5)
+    assert np.array_equal(T == 1.0, a["exited"] != 0)
+    hit = (a["ok"] != 0) & (a["exited"] == 0) & (a["t"] > 0)
+    assert hit.mean() > 0.3
+    # gradient at a hit points against the ray (GPM:303-308 rejects the others)
+    gd = (a["grad"] * rays["d"]).sum(1)
+    assert (gd[hit] <= 0).all()
+    # the field changes sign within one step after the reported crossing
+    o, d, t = rays["o"][hit][:4096], rays["d"][hit][:4096], a["t"][hit][:4096]
+    p0 = (o.astype(np.float64) + t[:, None] * d).astype(np.float32); p1 = (o.astype(np.float64) + (t[:, None] + 0.0101) * d).astype(np.float32)
+    v0 = gpu.eval(np.ascontiguousarray(p0), np.ascontiguousarray(d), gradient=False)["val"]; v1 = gpu.eval(np.ascontiguousarray(p1), np.ascontiguousarray(d), gradient=False)["val"]
+    assert ((v0 >= 0) & (v1 < 0)).mean() > 0.97  # camera rays start outside the sphere: sign0 = +1
+
+
+def test_edge_cases(torch_cuda):
+    """Empty batch, zero-length ray (maxT == 0), infinite farT, max_bounces reached, ragged sizes."""
+    mj = S.MEDIA["iso_3d_renewal"]
+    gpu, orc = S.GpuImpl(mj), S.CpuImpl("orc", mj)
+    rays, st = S.camera_rays(0)
+    out = gpu.sample_distance(rays, st, 1)
+    assert len(out["ok"]) == 0
+    for n in (1, 31, 33, 129):
+        rays, st = S.camera_rays(n, seed=n, secondary=True)
+        rays["tmax"][0] = 0.0; rays["tmin"][0] = 0.0  # maxT == 0: trivial exit (GPM:239-248)
+        if n > 2:
+            rays["tmax"][1] = np.inf; rays["tmin"][1] = 1990.0  # infinite ray: farT = nearT + 2000, 10 unit march
+            st["bounce"][2] = 1024  # bounce >= max_bounces: refused (GPM:235-237)
+        a, b = gpu.sample_distance(rays, st, 1), orc.sample_distance(rays, st, 1)
+        rep = S.compare_queries(a, b)
+        assert rep["decision_mismatch"] == 0 and rep["t_rel"] <= TOL and rep["grad_rel"] <= TOL, rep
+        assert a["ok"][0] == 1 and a["exited"][0] == 1 and a["t"][0] == 0
+        if n > 2:
+            assert a["ok"][2] == 0
