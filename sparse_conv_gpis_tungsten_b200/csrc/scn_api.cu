@@ -227,8 +227,8 @@ static void to_eval_in(const scn_eval_in *in, EvalIn &k) {
 
 int scn_eval_batch(const scn_medium *m, const scn_eval_in *in, const scn_eval_out *out, size_t n, int what, void *stream) {
     if (!m || !in || !out) return set_error(SCN_EINVAL, "null argument");
-    if (!in->px || !in->py || !in->pz || !in->dx || !in->dy || !in->dz) return set_error(SCN_EINVAL, "eval: points and directions are required");
     if (n == 0) return SCN_OK;
+    if (!in->px || !in->py || !in->pz || !in->dx || !in->dy || !in->dz) return set_error(SCN_EINVAL, "eval: points and directions are required");
     DeviceGuard g(m->device); if (!g.ok) return set_error(SCN_ECUDA, "cannot select device %d", m->device);
     cudaStream_t s = (cudaStream_t)stream;
     EvalIn ki; to_eval_in(in, ki);
@@ -277,6 +277,7 @@ static int to_state(const scn_state *s, State &k) {
 
 int scn_sample_distance_batch(const scn_medium *m, const scn_rays *rays, const scn_state *state, const scn_samples *out, size_t n, void *stream) {
     if (!m || !rays || !state || !out) return set_error(SCN_EINVAL, "null argument");
+    if (n == 0) return SCN_OK; // an empty wavefront is a no-op (empty buffers may be NULL)
     if (!out->ok || !out->exited || !out->t || !out->continued_t || !out->gx || !out->gy || !out->gz || !out->gp_id || !out->scheme || !out->weight)
         return set_error(SCN_EINVAL, "samples: every output but n_evals is required");
     Rays kr; State ks;
@@ -299,7 +300,9 @@ static int transmittance_impl(const scn_medium *m, const scn_rays *rays, const s
     return check_launch("k_transmittance");
 }
 int scn_transmittance_batch(const scn_medium *m, const scn_rays *rays, const scn_state *state, float *T_out, size_t n, void *stream) {
-    if (!m || !rays || !state || !T_out) return set_error(SCN_EINVAL, "null argument");
+    if (!m || !rays || !state) return set_error(SCN_EINVAL, "null argument");
+    if (n == 0) return SCN_OK;
+    if (!T_out) return set_error(SCN_EINVAL, "null argument");
     DeviceGuard g(m->device); if (!g.ok) return set_error(SCN_ECUDA, "cannot select device %d", m->device);
     return transmittance_impl(m, rays, state, T_out, nullptr, n, (cudaStream_t)stream);
 }
@@ -379,8 +382,8 @@ extern "C" {
 
 int scn_eval_batch_host(scn_medium *m, const scn_eval_in *in, const scn_eval_out *out, size_t n, int what) {
     if (!m || !in || !out) return set_error(SCN_EINVAL, "null argument");
-    if (!in->px || !in->py || !in->pz || !in->dx || !in->dy || !in->dz) return set_error(SCN_EINVAL, "eval: points and directions are required");
     if (n == 0) return SCN_OK;
+    if (!in->px || !in->py || !in->pz || !in->dx || !in->dy || !in->dz) return set_error(SCN_EINVAL, "eval: points and directions are required");
     std::lock_guard<std::mutex> lock(m->mu);
     DeviceGuard g(m->device); if (!g.ok) return set_error(SCN_ECUDA, "cannot select device %d", m->device);
     size_t chunk = n < HOST_CHUNK ? n : HOST_CHUNK;
@@ -418,6 +421,7 @@ int scn_eval_batch_host(scn_medium *m, const scn_eval_in *in, const scn_eval_out
 
 static int query_host(scn_medium *m, const scn_rays *rays, const scn_state *state, const scn_samples *out, float *T_out, size_t n) {
     if (!m || !rays || !state) return set_error(SCN_EINVAL, "null argument");
+    if (n == 0) return SCN_OK;
     Rays kr; State ks;
     if (int rc = to_rays(rays, kr)) return rc;
     if (int rc = to_state(state, ks)) return rc;

@@ -52,7 +52,7 @@ class _Args:
         if _is_torch(x):
             want = np.dtype(dtype)
             have = _TORCH_TO_NP.get(x.dtype)
-            if have is None and want == np.dtype(np.uint32) and x.dtype == torch.int32:
+            if want == np.dtype(np.uint32) and x.dtype == torch.int32:
                 have = want  # int32 storage reinterpreted as uint32
             if have != want:
                 raise TypeError("%s: expected %s, got %s" % (name, want, x.dtype))
