@@ -121,8 +121,10 @@ def test_microbench_full_size_properties(torch_cuda):
         assert torch.equal(a, b)
     assert bool(torch.isfinite(o1[0]).all())
     var = float(o1[0].double().var())
-    assert abs(var - 1.0) < 0.02, var
-    assert abs(float(o1[0].double().mean())) < 1e-3
+    # one realization of finite extent (the rotated lattices of all rays share the ~13^3 cells around the origin), so the
+    # spatial statistics fluctuate by a few per cent; the compiled reference gives var 0.962, mean 0.055 on these points
+    assert abs(var - 1.0) < 0.1, var
+    assert abs(float(o1[0].double().mean())) < 0.1
     idx = torch.arange(0, n, n // 2048, device="cuda")
     p = torch.stack([x[idx] for x in P], 1).cpu().numpy(); d = torch.stack([x[idx] for x in D], 1).cpu().numpy()
     orc = S.CpuImpl("orc", mj)
