@@ -8,11 +8,14 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <cstdlib>
 #include <mutex>
 #include <new>
 
 #include "scn_device.cuh"
 #include "scn_fast.cuh"
+#include "scn_march.cuh"
+#include <atomic>
 
 namespace scn {
 
@@ -71,9 +74,6 @@ __global__ void __launch_bounds__(BLOCK) k_conditioning(const __grid_constant__ 
     a.ctx[0][i] = c.vs; a.ctx[1][i] = c.gs.x; a.ctx[2][i] = c.gs.y; a.ctx[3][i] = c.gs.z; a.ctx[4][i] = c.org.x; a.ctx[5][i] = c.org.y; a.ctx[6][i] = c.org.z;
 }
 
-struct Rays { const float *ox, *oy, *oz, *dx, *dy, *dz, *tmin, *tmax, *u; const uint32_t *px, *py, *spp, *seg; uint32_t scene_seed; };
-struct State { uint8_t *first_scatter; float *last_val, *lgx, *lgy, *lgz; int32_t *bounce, *last_gp_id; float *info_t; uint8_t *scheme; float *ctx[7]; };
-struct Samples { uint8_t *ok, *exited; float *t, *cont_t, *gx, *gy, *gz; int32_t *gp_id; uint8_t *scheme; float *weight; uint32_t *n_evals; };
 
 __device__ __forceinline__ RayState load_state(const State &s, const Rays &r, size_t i) {
     RayState st;
@@ -175,6 +175,12 @@ struct scn_medium {
     cudaStream_t streams[3] = {nullptr, nullptr, nullptr};
     char *arena[3] = {nullptr, nullptr, nullptr};
     size_t arena_cap = 0;
+    // k_march: ring of ray counters (one per launch in flight, zeroed in-stream before the launch) and the SM count
+    static constexpr unsigned COUNTERS = 1024;
+    unsigned int *counters = nullptr;
+    mutable std::atomic<unsigned> next_counter{0};
+    int sm_count = 0;
+    int march_block = 0; // 128 / 64, 0 = generic kernels only
 };
 
 static inline unsigned grid_for(size_t n) { return (unsigned)((n + BLOCK - 1) / BLOCK); }
@@ -185,6 +191,25 @@ struct DeviceGuard {
     explicit DeviceGuard(int dev) { if (cudaGetDevice(&prev) != cudaSuccess) { ok = false; return; } if (prev != dev && cudaSetDevice(dev) != cudaSuccess) ok = false; }
     ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
 };
+
+// cached wavefront march (scn_march.cuh) for the configurations it covers; SCN_FORCE_GENERIC=1 keeps the generic walk
+static bool use_march(const scn_medium *m) {
+    static const bool forced = [] { const char *e = getenv("SCN_FORCE_GENERIC"); return e && e[0] == '1'; }();
+    return m->march_block != 0 && !forced;
+}
+template <bool TRANSMIT>
+static int launch_march(const scn_medium *m, const Rays &kr, const State &ks, const Samples &ko, float *T, uint32_t *n_evals, size_t n, cudaStream_t s) {
+    for (size_t b = 0; b < n; b += 0x40000000u) { // the ray counter is 32 bits wide
+        unsigned c = (unsigned)(n - b < 0x40000000u ? n - b : 0x40000000u);
+        MarchArgs A; A.r = kr; A.s = ks; A.o = ko; A.T = T; A.n_evals = n_evals; A.n = c; A.K = march_cache_entries(m->P.n_imp);
+        if (b) { return set_error(SCN_EINVAL, "batches above 2^30 rays are not supported"); }
+        A.counter = m->counters + (m->next_counter.fetch_add(1) % scn_medium::COUNTERS);
+        SCN_CUDA(cudaMemsetAsync(A.counter, 0, sizeof(unsigned int), s));
+        cudaError_t e = m->march_block == 128 ? launch_march_t<128, TRANSMIT>(m->P, A, m->sm_count, s) : launch_march_t<64, TRANSMIT>(m->P, A, m->sm_count, s);
+        if (e != cudaSuccess) return cuda_fail(e, "k_march");
+    }
+    return SCN_OK;
+}
 
 extern "C" {
 
@@ -205,6 +230,13 @@ int scn_medium_create(const scn_medium_desc *desc, int device, scn_medium **out)
     scn_medium *m = new (std::nothrow) scn_medium();
     if (!m) return set_error(SCN_ENOMEM, "out of memory");
     m->desc = *desc; m->P = P; m->device = device;
+    m->march_block = march_block_size(P);
+    {
+        DeviceGuard g(device);
+        cudaError_t e1 = cudaDeviceGetAttribute(&m->sm_count, cudaDevAttrMultiProcessorCount, device);
+        cudaError_t e2 = cudaMalloc((void **)&m->counters, scn_medium::COUNTERS * sizeof(unsigned int));
+        if (e1 != cudaSuccess || e2 != cudaSuccess) { delete m; return cuda_fail(e1 != cudaSuccess ? e1 : e2, "scn_medium_create"); }
+    }
     *out = m;
     return SCN_OK;
 }
@@ -214,6 +246,7 @@ void scn_medium_destroy(scn_medium *m) {
     {
         DeviceGuard g(m->device);
         for (int i = 0; i < 3; ++i) { if (m->arena[i]) cudaFree(m->arena[i]); if (m->streams[i]) cudaStreamDestroy(m->streams[i]); }
+        if (m->counters) cudaFree(m->counters);
     }
     delete m;
 }
@@ -287,6 +320,7 @@ int scn_sample_distance_batch(const scn_medium *m, const scn_rays *rays, const s
     DeviceGuard g(m->device); if (!g.ok) return set_error(SCN_ECUDA, "cannot select device %d", m->device);
     Samples ko; ko.ok = out->ok; ko.exited = out->exited; ko.t = out->t; ko.cont_t = out->continued_t; ko.gx = out->gx; ko.gy = out->gy; ko.gz = out->gz;
     ko.gp_id = out->gp_id; ko.scheme = out->scheme; ko.weight = out->weight; ko.n_evals = out->n_evals;
+    if (use_march(m)) return launch_march<false>(m, kr, ks, ko, nullptr, nullptr, n, (cudaStream_t)stream);
     k_sample_distance<<<grid_for(n), BLOCK, 0, (cudaStream_t)stream>>>(m->P, kr, ks, ko, n);
     return check_launch("k_sample_distance");
 }
@@ -296,6 +330,7 @@ static int transmittance_impl(const scn_medium *m, const scn_rays *rays, const s
     if (int rc = to_rays(rays, kr)) return rc;
     if (int rc = to_state(state, ks)) return rc;
     if (n == 0) return SCN_OK;
+    if (use_march(m)) { Samples none{}; return launch_march<true>(m, kr, ks, none, T, n_evals, n, s); }
     k_transmittance<<<grid_for(n), BLOCK, 0, s>>>(m->P, kr, ks, T, n_evals, n);
     return check_launch("k_transmittance");
 }

@@ -43,20 +43,23 @@ __device__ __forceinline__ void lcg_step(uint32_t &lo, uint32_t &hi, uint64_t in
 }
 // PCG XSH-RR output of the state (lo, hi): xs = bits [27,59) of s ^ (s >> 18), rotated right by s >> 59
 __device__ __forceinline__ uint32_t pcg_out(uint32_t lo, uint32_t hi) {
-    uint32_t xs = __funnelshift_r(lo, hi, 27) ^ (hi >> 13);
-    return __funnelshift_r(xs, xs, hi >> 27);
+    // the two plain shifts of `hi` go through IMAD.HI (FMA pipe): the ALU pipe (SHF/LOP3/LEA) is the fullest pipe of this loop
+    uint32_t xs = __funnelshift_r(lo, hi, 27) ^ __umulhi(hi, 1u << 19);
+    return __funnelshift_r(xs, xs, __umulhi(hi, 1u << 5));
 }
 __device__ __forceinline__ float ex2_approx(float x) { float y; asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
 
 // All N impulses of one cell (cell3D, SCN:375-395) against the point whose cell-local coordinates are (cx, cy, cz).
 // ISO_A: the kernel's inverse covariance is a multiple of the identity in the sampling space (a0 only).
-template <bool ISO_A>
-__device__ __forceinline__ void cell_accumulate(uint32_t h, uint32_t nimp, uint64_t inc, float cx, float cy, float cz, float a0, float a1, float a2,
+// NIMP > 0: the impulse count is a compile-time constant and the loop is unrolled (no loop-control instructions).
+template <bool ISO_A, int NIMP>
+__device__ __forceinline__ void cell_accumulate(uint32_t h, uint32_t nimp_dyn, uint64_t inc, float cx, float cy, float cz, float a0, float a1, float a2,
                                                 float &sv, float &s0, float &s1, float &s2) {
     // set_state(h + 1u) (the +1 wraps in 32 bits), then two discarded draws (sampling/UniformSampler.hpp:71-75)
     uint32_t lo = h + 1u, hi = 0u;
     lcg_step(lo, hi, inc); lcg_step(lo, hi, inc);
-#pragma unroll 1
+    const uint32_t nimp = NIMP > 0 ? (uint32_t)NIMP : nimp_dyn;
+#pragma unroll(NIMP > 0 ? NIMP : 1)
     for (uint32_t k = 0; k < nimp; ++k) {
         // next3D draws z, y, x (g++ argument order), then the Bernoulli sign (SCN:384-385)
         const float uz = u32_to_unit(pcg_out(lo, hi)); lcg_step(lo, hi, inc);
@@ -74,7 +77,7 @@ __device__ __forceinline__ void cell_accumulate(uint32_t h, uint32_t nimp, uint6
     }
 }
 
-template <bool ISO>
+template <bool ISO, int NIMP>
 __global__ void __launch_bounds__(FAST_BLOCK) k_fast_noise3d(const __grid_constant__ Params P, const float *__restrict__ px, const float *__restrict__ py,
                                                              const float *__restrict__ pz, const float *__restrict__ dx, const float *__restrict__ dy,
                                                              const float *__restrict__ dz, uint32_t seed, uint64_t inc, float *__restrict__ oval,
@@ -122,8 +125,8 @@ __global__ void __launch_bounds__(FAST_BLOCK) k_fast_noise3d(const __grid_consta
                 const float cx = ddx < 0 ? cxm : (ddx == 0 ? cx0 : cxp);
                 const uint32_t h = xx_final(XP4 * rotl17(hy + (uint32_t)(ix + ddx) * XP3));
                 float cv = 0.f, c0 = 0.f, c1 = 0.f, c2 = 0.f;
-                if (iso_a) cell_accumulate<true>(h, nimp, inc, cx, cy, cz, A0, A1, A2, cv, c0, c1, c2);
-                else cell_accumulate<false>(h, nimp, inc, cx, cy, cz, A0, A1, A2, cv, c0, c1, c2);
+                if (iso_a) cell_accumulate<true, NIMP>(h, nimp, inc, cx, cy, cz, A0, A1, A2, cv, c0, c1, c2);
+                else cell_accumulate<false, NIMP>(h, nimp, inc, cx, cy, cz, A0, A1, A2, cv, c0, c1, c2);
                 sv += cv; s0 += c0; s1 += c1; s2 += c2;
             }
         }
@@ -145,8 +148,12 @@ inline void launch_fast_noise3d(const Params &P, const float *px, const float *p
                                 uint32_t seed, float *oval, float *ogx, float *ogy, float *ogz, size_t n, cudaStream_t s) {
     unsigned grid = (unsigned)((n + FAST_BLOCK - 1) / FAST_BLOCK);
     const uint64_t inc = 1ULL; // the PCG32 stream increment (_sequence | 1, sampling/UniformSampler.hpp:17-27)
-    if (P.iso3d) k_fast_noise3d<true><<<grid, FAST_BLOCK, 0, s>>>(P, px, py, pz, dx, dy, dz, seed, inc, oval, ogx, ogy, ogz, n);
-    else k_fast_noise3d<false><<<grid, FAST_BLOCK, 0, s>>>(P, px, py, pz, dx, dy, dz, seed, inc, oval, ogx, ogy, ogz, n);
+#define SCN_FAST_LAUNCH(ISO_, N_) k_fast_noise3d<ISO_, N_><<<grid, FAST_BLOCK, 0, s>>>(P, px, py, pz, dx, dy, dz, seed, inc, oval, ogx, ogy, ogz, n)
+#define SCN_FAST_BY_N(ISO_) switch (P.n_imp) { case 1: SCN_FAST_LAUNCH(ISO_, 1); break; case 2: SCN_FAST_LAUNCH(ISO_, 2); break; case 3: SCN_FAST_LAUNCH(ISO_, 3); break; \
+                                               case 4: SCN_FAST_LAUNCH(ISO_, 4); break; default: SCN_FAST_LAUNCH(ISO_, 0); }
+    if (P.iso3d) { SCN_FAST_BY_N(true) } else { SCN_FAST_BY_N(false) }
+#undef SCN_FAST_BY_N
+#undef SCN_FAST_LAUNCH
 }
 #endif // __CUDACC__
 
