@@ -205,7 +205,7 @@ static int launch_march(const scn_medium *m, const Rays &kr, const State &ks, co
         if (b) { return set_error(SCN_EINVAL, "batches above 2^30 rays are not supported"); }
         A.counter = m->counters + (m->next_counter.fetch_add(1) % scn_medium::COUNTERS);
         SCN_CUDA(cudaMemsetAsync(A.counter, 0, sizeof(unsigned int), s));
-        cudaError_t e = m->march_block == 128 ? launch_march_t<128, TRANSMIT>(m->P, A, m->sm_count, s) : launch_march_t<64, TRANSMIT>(m->P, A, m->sm_count, s);
+        cudaError_t e = launch_march_t<TRANSMIT>(m->P, A, m->march_block, m->sm_count, s);
         if (e != cudaSuccess) return cuda_fail(e, "k_march");
     }
     return SCN_OK;

@@ -1,6 +1,7 @@
 set -x; mkdir -p gpurun_out
-timeout 900 python -m pytest tests -m gpu -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?" >> gpurun_out/pytest_gpu.log
-tail -30 gpurun_out/pytest_gpu.log
-for m in c1_sphere_3d_none world_3d_none iso_3d_renewalplus_aniso; do timeout 300 python tools/run_queries.py $m 20 2; timeout 300 python tools/run_queries.py $m 20 2 secondary; done > gpurun_out/queries_all.log 2>&1
+timeout 900 python -m pytest tests -m gpu -q -x > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?" >> gpurun_out/pytest_gpu.log
+tail -15 gpurun_out/pytest_gpu.log
+for m in c1_sphere_3d_none world_3d_none; do timeout 300 python tools/run_queries.py $m 20 2; timeout 300 python tools/run_queries.py $m 20 2 secondary; done > gpurun_out/queries_all.log 2>&1
 cat gpurun_out/queries_all.log
-timeout 600 python bench.py --steps 3 --warmup 3 > gpurun_out/bench_full.json 2> gpurun_out/bench_full.err; tail -3 gpurun_out/bench_full.err
+Q="python tools/run_queries.py c1_sphere_3d_none 18 2"
+$Q > gpurun_out/queries_plain.log 2>&1 && ncu --set full --clock-control none --import-source on -k regex:k_march -s 1 -c 1 -o gpurun_out/prof_march $Q > gpurun_out/ncu3.log 2>&1
