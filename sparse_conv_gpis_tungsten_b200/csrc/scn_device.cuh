@@ -21,7 +21,7 @@
 #define SCN_HD __host__ __device__ __forceinline__
 // Large bodies (the impulse loops and everything that calls them more than once) are real functions on the device:
 // forcing them inline multiplies the 27-cell loop nest dozens of times and takes ptxas tens of minutes.
-#define SCN_FN __host__ __device__ __noinline__
+#define SCN_FN inline __host__ __device__ __noinline__
 #else
 #define SCN_HD inline
 #define SCN_FN inline

@@ -1,0 +1,192 @@
+"""Host side of the wavefront batching stage (include/scn_render.h): the loop PathTracer::traceSample runs per path
+(integrators/path_tracer/PathTracer.cpp:62-169) run per WAVEFRONT, and the tile scheduling of PathTraceIntegrator
+(integrators/path_tracer/PathTraceIntegrator.cpp:26-41, 135-163, 227-246) with GPUs in place of pool threads: every rank owns a
+contiguous range of the 16 x 16 tiles and the framebuffer slice of those tiles; the only collective is one all_gather of the
+slices at the end of the render (`gather_image`).  torch is plumbing here: device buffers, streams, torch.distributed.
+
+Nothing in this module computes radiance: rays, shading and accumulation are the CUDA kernels of csrc/scn_render.cu, the medium
+query is scn_sample_distance_batch.  There is no CPU fallback.
+"""
+import ctypes as C
+
+import numpy as np
+import torch
+
+from . import abi
+from .medium import CTX_NAMES, RAY_F, RAY_U, SAMPLE_FIELDS, STATE_FIELDS, SparseConvolutionNoiseMedium
+
+TILE = 16
+
+
+class WfScene(C.Structure):
+    _fields_ = [("cam_pos", C.c_float * 3), ("cam_look_at", C.c_float * 3), ("cam_up", C.c_float * 3), ("fov_deg", C.c_float),
+                ("res_x", C.c_uint32), ("res_y", C.c_uint32), ("cube_center", C.c_float * 3), ("cube_half", C.c_float * 3),
+                ("emission", C.c_float), ("albedo", C.c_float), ("max_bounces", C.c_int32), ("scene_seed", C.c_uint32)]
+
+
+class WfPaths(C.Structure):
+    _fields_ = [("rays", abi.Rays), ("state", abi.State), ("samples", abi.Samples), ("throughput", abi.f32p), ("radiance", abi.f32p), ("alive", abi.u8p)]
+
+
+RENDER_SYMBOLS = {
+    "scn_wf_tile_count": (C.c_uint32, [C.c_uint32, C.c_uint32]),
+    "scn_wf_raygen": (C.c_int, [C.POINTER(WfScene), abi.MediumP, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.POINTER(WfPaths), C.c_size_t, C.c_void_p]),
+    "scn_wf_shade": (C.c_int, [C.POINTER(WfScene), abi.MediumP, C.POINTER(WfPaths), C.c_size_t, C.c_int32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p]),
+    "scn_wf_accumulate": (C.c_int, [abi.f32p, abi.f32p, C.c_size_t, C.c_uint32, C.c_void_p]),
+}
+
+
+def load():
+    lib = abi.load()
+    for name, (res, args) in RENDER_SYMBOLS.items():
+        fn = getattr(lib, name)
+        fn.restype = res
+        fn.argtypes = args
+    return lib
+
+
+def scene_from_json(scene):
+    """The restricted scene out of a Tungsten scene dict: pinhole camera, one cube holding the medium,
+    constant infinite_sphere, lambert albedo of the medium's brdf phase function, integrator max_bounces."""
+    s = WfScene()
+    cam = scene["camera"]
+    tr = cam.get("transform", {})
+    s.cam_pos[:] = tr.get("position", [0, 0, 5]); s.cam_look_at[:] = tr.get("look_at", [0, 0, 0]); s.cam_up[:] = tr.get("up", [0, 1, 0])
+    s.fov_deg = float(cam.get("fov", 60.0))
+    res = cam.get("resolution", [64, 64])
+    s.res_x, s.res_y = (int(res), int(res)) if np.isscalar(res) else (int(res[0]), int(res[1]))
+    cube = next(p for p in scene["primitives"] if p["type"] == "cube")
+    ctr = cube.get("transform", {})
+    scale = ctr.get("scale", [1, 1, 1])
+    scale = [scale] * 3 if np.isscalar(scale) else scale
+    s.cube_center[:] = ctr.get("position", [0, 0, 0]); s.cube_half[:] = [0.5 * float(v) for v in scale]
+    env = next((p for p in scene["primitives"] if p["type"] == "infinite_sphere"), None)
+    em = env.get("emission", 1.0) if env else 0.0
+    s.emission = float(em if np.isscalar(em) else np.mean(em))
+    med = scene["media"][0]
+    alb = med.get("phase_function", {}).get("bsdf", {}).get("albedo", 1.0)
+    s.albedo = float(alb if np.isscalar(alb) else np.mean(alb))
+    s.max_bounces = int(scene.get("integrator", {}).get("max_bounces", 64))
+    s.scene_seed = int(scene.get("renderer", {}).get("seed", 0xBA5EBA11)) & 0xFFFFFFFF
+    return s
+
+
+def tile_range(n_tiles, rank, world):
+    """Contiguous tile range of a rank: tiles in diceTiles order split into `world` near-equal ranges."""
+    base, rem = divmod(n_tiles, world)
+    first = rank * base + min(rank, rem)
+    return first, base + (1 if rank < rem else 0)
+
+
+class WavefrontRenderer:
+    """One GPU's share of a render: tiles [tile_first, tile_first + tile_count)."""
+
+    def __init__(self, scene_json, device=0, rank=0, world=1, max_paths=1 << 22):
+        self.lib = load()
+        self.scene = scene_from_json(scene_json)
+        self.dev = torch.device("cuda", device)
+        self.medium = SparseConvolutionNoiseMedium.from_json(scene_json["media"][0], device)
+        self.n_tiles = int(self.lib.scn_wf_tile_count(self.scene.res_x, self.scene.res_y))
+        self.tile_first, self.tile_count = tile_range(self.n_tiles, rank, world)
+        self.n_pixels = self.tile_count * TILE * TILE
+        self.max_paths = max_paths
+        self.framebuffer = torch.zeros(max(self.n_pixels, 1), dtype=torch.float32, device=self.dev)
+        self.spp_done = 0
+        self.queries = 0
+        self._buf_n = 0
+
+    def _alloc(self, n):
+        if n == self._buf_n:
+            return
+        tdt = {np.float32: torch.float32, np.int32: torch.int32, np.uint8: torch.uint8, np.uint32: torch.int32}
+        mk = lambda dt: torch.empty(n, dtype=tdt[dt], device=self.dev)
+        self.rays = {k: mk(np.float32) for k in RAY_F}
+        self.rays.update({k: mk(np.uint32) for k in RAY_U})
+        self.state = {k: mk(dt) for k, dt in STATE_FIELDS}
+        self.state["scheme"] = mk(np.uint8)
+        self.state.update({k: mk(np.float32) for k in CTX_NAMES})
+        self.samples = {k: mk(dt) for k, dt in SAMPLE_FIELDS}
+        self.throughput, self.radiance, self.alive = mk(np.float32), mk(np.float32), mk(np.uint8)
+        p = WfPaths()
+        ptr = lambda t, ct: C.cast(C.c_void_p(t.data_ptr()), ct)
+        for k in RAY_F:
+            setattr(p.rays, k, ptr(self.rays[k], abi.f32p))
+        for k in RAY_U:
+            setattr(p.rays, k, ptr(self.rays[k], abi.u32p))
+        p.rays.scene_seed = self.scene.scene_seed
+        ct = {np.float32: abi.f32p, np.int32: abi.i32p, np.uint8: abi.u8p}
+        for k, dt in STATE_FIELDS:
+            setattr(p.state, k, ptr(self.state[k], ct[dt]))
+        p.state.scheme = ptr(self.state["scheme"], abi.u8p)
+        for i, k in enumerate(CTX_NAMES):
+            p.state.ctx[i] = ptr(self.state[k], abi.f32p)
+        for k, dt in SAMPLE_FIELDS:
+            setattr(p.samples, k, ptr(self.samples[k], ct[dt]))
+        p.throughput, p.radiance, p.alive = ptr(self.throughput, abi.f32p), ptr(self.radiance, abi.f32p), ptr(self.alive, abi.u8p)
+        self.paths = p
+        self._buf_n = n
+
+    def render(self, spp, count_queries=False):
+        """Add `spp` samples per pixel to this rank's framebuffer slice.  Samples are processed in chunks so that a wavefront
+        holds at most max_paths paths."""
+        if self.n_pixels == 0:
+            return
+        stream = torch.cuda.current_stream(self.dev)
+        sp = C.c_void_p(stream.cuda_stream)
+        chunk = max(1, min(spp, self.max_paths // self.n_pixels))
+        done = 0
+        while done < spp:
+            c = min(chunk, spp - done)
+            n = self.n_pixels * c
+            self._alloc(n)
+            abi.check(self.lib.scn_wf_raygen(C.byref(self.scene), self.medium._h, self.tile_first, self.tile_count, self.spp_done + done, c, C.byref(self.paths), n, sp))
+            for bounce in range(self.scene.max_bounces):
+                if count_queries:
+                    self.queries += int(self.alive.sum().item())
+                self.medium.sample_distance(self.rays, self.state, scene_seed=self.scene.scene_seed, out=self.samples, stream=stream)
+                abi.check(self.lib.scn_wf_shade(C.byref(self.scene), self.medium._h, C.byref(self.paths), n, bounce, self.spp_done + done, c, self.tile_first, sp))
+            abi.check(self.lib.scn_wf_accumulate(C.cast(C.c_void_p(self.radiance.data_ptr()), abi.f32p), C.cast(C.c_void_p(self.framebuffer.data_ptr()), abi.f32p),
+                                                 self.n_pixels, c, sp))
+            done += c
+        self.spp_done += spp
+
+    def local_image(self):
+        """This rank's tiles as [tile_count, 16, 16] mean radiance."""
+        return (self.framebuffer[: self.n_pixels] / max(self.spp_done, 1)).view(self.tile_count, TILE, TILE)
+
+    def close(self):
+        self.medium.close()
+
+
+def assemble_image(tiles, res_x, res_y):
+    """[n_tiles, 16, 16] in diceTiles order -> [res_y, res_x] (edge tiles cropped)."""
+    tx, ty = (res_x + TILE - 1) // TILE, (res_y + TILE - 1) // TILE
+    img = tiles.view(ty, tx, TILE, TILE).permute(0, 2, 1, 3).reshape(ty * TILE, tx * TILE)
+    return img[:res_y, :res_x].contiguous()
+
+
+def gather_image(renderer, world=1):
+    """The one collective of a render: all ranks' framebuffer slices -> the full image on every rank (NCCL all_gather over
+    NVLink; 4 B per pixel).  Slices are padded to the largest tile count so that the gather is a single call."""
+    local = renderer.local_image()
+    if world > 1:
+        import torch.distributed as dist
+        cap = (renderer.n_tiles + world - 1) // world
+        pad = torch.zeros(cap, TILE, TILE, dtype=torch.float32, device=local.device)
+        pad[: local.shape[0]] = local
+        out = [torch.empty_like(pad) for _ in range(world)]
+        dist.all_gather(out, pad)
+        parts = [out[r][: tile_range(renderer.n_tiles, r, world)[1]] for r in range(world)]
+        tiles = torch.cat(parts, 0)
+    else:
+        tiles = local
+    return assemble_image(tiles, renderer.scene.res_x, renderer.scene.res_y)
+
+
+def write_pfm(path, img):
+    """PFM writer matching the reference's HDR output (io/ImageIO.cpp savePfm): bottom-up rows, little-endian, 3 channels."""
+    a = np.asarray(img, dtype=np.float32)
+    rgb = np.repeat(a[::-1, :, None], 3, axis=2)
+    with open(path, "wb") as f:
+        f.write(b"PF\n%d %d\n-1.0\n" % (a.shape[1], a.shape[0]))
+        f.write(rgb.astype("<f4").tobytes())
