@@ -208,6 +208,30 @@ def run_gpu(args):
     e2e_value = world * ne * e2e_steps / float(te.item())
     same = all(torch.equal(a, b[:ne].cpu()) for a, b in zip(ho, outs))
 
+    # ---- tile-sharded wavefront render: every rank renders its contiguous tile range, one NCCL all_gather of the slices
+    render = None
+    if not args.no_extras:
+        from sparse_conv_gpis_tungsten_b200 import render as R
+        res, spp = 512, 16
+        sc = {"media": [S.MEDIA["c1_sphere_3d_none"]],
+              "primitives": [{"type": "cube", "transform": {"scale": [3, 3, 3]}, "bsdf": {"type": "forward"}, "int_medium": "gpis"},
+                             {"type": "infinite_sphere", "emission": 1.0, "sample": True}],
+              "camera": {"type": "pinhole", "resolution": [res, res], "fov": 35, "transform": {"position": [0, 0, 5], "look_at": [0, 0, 0], "up": [0, 1, 0]}},
+              "integrator": {"type": "path_tracer", "max_bounces": 8}, "renderer": {"spp": spp, "adaptive_sampling": False}}
+        wr = R.WavefrontRenderer(sc, device=local, rank=rank, world=world); wr.render(1); wr.close()  # warm-up
+        wr = R.WavefrontRenderer(sc, device=local, rank=rank, world=world)
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record(stream); wr.render(spp); img = R.gather_image(wr, world); b.record(stream); torch.cuda.synchronize()
+        tr = torch.tensor([a.elapsed_time(b)], device=dev, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(tr, op=dist.ReduceOp.MAX)
+        render = {"workload": "C1 scene (Appendix A.1) %dx%d @%dspp, max_bounces 8, 16x16 tiles sharded over %d GPU(s), one all_gather" % (res, res, spp, world),
+                  "ms": float(tr.item()), "camera_paths_per_s": res * res * spp / (float(tr.item()) * 1e-3), "mean_radiance": float(img.mean().item())}
+        wr.close()
+
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -228,7 +252,7 @@ def run_gpu(args):
     ach_issue = per_gpu * w_issue(DENSITY)
     hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
     roofline = {"bound": "fp32-issue", "achieved": ach_issue / 1e12, "peak": issue_peak / 1e12, "unit": "Tlane-op/s", "frac": ach_issue / issue_peak,
-                "traffic": None, "kernel": "k_fast_noise3d<ISO>", "avg_launch_ms": ms_max / args.steps,
+                "traffic": None, "kernel": "k_fast_noise3d<ISO=%d, NIMP=%d>" % (int(ISO), DENSITY), "avg_launch_ms": ms_max / args.steps,
                 "algorithmic": {"lane_ops_per_eval": w_issue(DENSITY), "flops_per_eval": w_flop(DENSITY), "bytes_per_eval": 40, "evals_per_launch": n},
                 "fp32_flops": {"achieved": per_gpu * w_flop(DENSITY) / 1e12, "peak": fp32_peak / 1e12, "unit": "TFLOP/s", "frac": per_gpu * w_flop(DENSITY) / fp32_peak},
                 "hbm": {"achieved": per_gpu * 40 / 1e9, "peak": hbm_peak, "unit": "GB/s", "frac": per_gpu * 40 / 1e9 / hbm_peak,
@@ -237,6 +261,8 @@ def run_gpu(args):
 
     # ---- extras: density sweep, world space, medium queries / s (configs[0]-style rays); one pass each, outside the timed region
     extra = {"e2e_matches_device": bool(same)}
+    if render is not None:
+        extra["render"] = render
     if not args.no_extras:
         sweep = {}
         for iso in (True, False):
@@ -265,6 +291,19 @@ def run_gpu(args):
         extra["medium_queries"] = {"workload": "C1 medium (sphere mean, SE, 3D iso, none/single), 2^20 camera rays, step 0.01",
                                    "queries_per_s": nq / qs, "noise_evals_per_s": ev / qs, "evals_per_query": ev / nq}
         g.close()
+        extra["medium_queries"]["kernel"] = "k_march (cached wavefront march)"
+        g = S.GpuImpl(S.MEDIA["c5_multires_nonstat_renewalplus"], device=local)
+        r, s = g._rays_state(rays, st)
+        out = g.m.sample_distance(r, s, scene_seed=1, count_evals=True)
+        torch.cuda.synchronize()
+        r, s = g._rays_state(rays, st)
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record(stream); out = g.m.sample_distance(r, s, scene_seed=1, out=out, stream=stream); b.record(stream); torch.cuda.synchronize()
+        qs = a.elapsed_time(b) * 1e-3
+        ev = int(out["n_evals"].view(torch.int32).to(torch.int64).sum().item())
+        extra["medium_queries_c5"] = {"workload": "C5 medium (multi-resolution non-stationary, renewal+), 2^20 camera rays, step 0.01",
+                                      "queries_per_s": nq / qs, "noise_evals_per_s": ev / qs, "evals_per_query": ev / nq}
+        g.close()
 
     # ---- CPU baseline on this box's host cores (bounded sample)
     threads = os.cpu_count() or 1
@@ -290,10 +329,24 @@ def run_gpu(args):
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": 24 * ne, "d2h_bytes_per_step": 16 * ne, "points_per_step": ne,
                     "api": "scn_eval_batch_host (pinned host buffers, 3-stream chunked pipeline)"},
             "gpu_launches": args.steps, "extra": extra}
-    print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
-    return 0
+    return line
+
+
+class StdoutToStderr:
+    """Anything libraries print on fd 1 during the run (NCCL's version banner, ...) goes to stderr: stdout carries ONE JSON line."""
+
+    def __enter__(self):
+        sys.stdout.flush()
+        self.saved = os.dup(1)
+        os.dup2(2, 1)
+        return self
+
+    def __exit__(self, *exc):
+        sys.stdout.flush()
+        os.dup2(self.saved, 1)
+        os.close(self.saved)
 
 
 def main():
@@ -308,7 +361,11 @@ def main():
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
-    return run_gpu(args)
+    with StdoutToStderr():
+        line = run_gpu(args)
+    if isinstance(line, dict):
+        print(json.dumps(line), flush=True)
+    return 0
 
 
 if __name__ == "__main__":

@@ -43,6 +43,15 @@ def test_tile_partition_and_assembly():
     assert np.array_equal(img.numpy(), (1000 * yy + xx).astype(np.float32))
 
 
+def test_render_header_symbols_exported():
+    import re
+    from sparse_conv_gpis_tungsten_b200 import render as R
+    hdr = open(os.path.join(S.ROOT, "include", "scn_render.h")).read()
+    declared = set(re.findall(r"^(?:int|uint32_t)\s+(scn_wf_\w+)\s*\(", hdr, re.M))
+    assert declared == set(R.RENDER_SYMBOLS), declared ^ set(R.RENDER_SYMBOLS)
+    R.load()  # binds every symbol: AttributeError if the library does not export one
+
+
 def test_pfm_writer(tmp_path):
     from sparse_conv_gpis_tungsten_b200 import render as R
     img = np.arange(12, dtype=np.float32).reshape(3, 4)

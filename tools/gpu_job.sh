@@ -1,6 +1,10 @@
 set -x; mkdir -p gpurun_out
-timeout 900 python -m pytest tests -m gpu -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?" >> gpurun_out/pytest_gpu.log
-tail -25 gpurun_out/pytest_gpu.log
-for c in c1 c5; do timeout 600 python tools/render.py --config $c --res 256 --spp 16 --out gpurun_out/$c.pfm; timeout 600 python tools/render.py --config $c --res 256 --spp 16 --count-queries; done > gpurun_out/render.log 2>&1
-cat gpurun_out/render.log
-for m in c5_multires_nonstat_renewalplus; do timeout 300 python tools/run_queries.py $m 20 2; done
+N=${NG:-2}
+TR="python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29511"
+timeout 600 python bench.py --steps 3 --warmup 3 > gpurun_out/bench_n1.json 2> gpurun_out/bench_n1.err; tail -2 gpurun_out/bench_n1.err
+timeout 600 $TR bench.py --gpus $N --steps 3 --warmup 3 > gpurun_out/bench_n$N.json 2> gpurun_out/bench_n$N.err; tail -3 gpurun_out/bench_n$N.err
+timeout 600 python tools/render.py --config c1 --res 1024 --spp 16 > gpurun_out/render_scale.log 2>&1
+timeout 600 $TR tools/render.py --config c1 --res 1024 --spp 16 >> gpurun_out/render_scale.log 2>&1
+timeout 600 python tools/render.py --config c5 --res 1024 --spp 16 >> gpurun_out/render_scale.log 2>&1
+timeout 600 $TR tools/render.py --config c5 --res 1024 --spp 16 >> gpurun_out/render_scale.log 2>&1
+grep workload gpurun_out/render_scale.log
