@@ -8,7 +8,7 @@ import ctypes as C
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libscn_b200.so")
+LIB_PATH = os.environ.get("SCN_LIB_PATH") or os.path.join(HERE, "libscn_b200.so")  # the override is a developer switch for A/B builds
 
 SCN_OK, SCN_EINVAL, SCN_EJSON, SCN_EUNSUPPORTED, SCN_ECUDA, SCN_ENOMEM = 0, -1, -2, -3, -4, -5
 CTX_GLOBAL, CTX_RENEWAL_PLUS, CTX_RENEWAL, CTX_NONE = 0, 1, 2, 3

@@ -26,6 +26,9 @@ inline bool fast_noise3d_supported(const Params &P) { return P.stationary && !P.
 constexpr int FAST_BLOCK = 128;
 
 #if defined(__CUDACC__)
+#ifndef SCN_LCG_JUMP
+#define SCN_LCG_JUMP 1
+#endif
 // One PCG32 state transition s' = s * 6364136223846793005 + 1 on a (lo, hi) register pair: IMAD.WIDE + 2 IMAD.
 // `inc` is the 64-bit increment (1) held in a register pair; it comes in as a kernel argument so that ptxas keeps
 // it resident instead of re-materialising two MOVs in front of every IMAD.WIDE.
@@ -43,11 +46,55 @@ __device__ __forceinline__ void lcg_step(uint32_t &lo, uint32_t &hi, uint64_t in
 }
 // PCG XSH-RR output of the state (lo, hi): xs = bits [27,59) of s ^ (s >> 18), rotated right by s >> 59
 __device__ __forceinline__ uint32_t pcg_out(uint32_t lo, uint32_t hi) {
-    // the two plain shifts of `hi` go through IMAD.HI (FMA pipe): the ALU pipe (SHF/LOP3/LEA) is the fullest pipe of this loop
+    // SCN_PCG_VARIANT picks which of the two plain shifts of `hi` go through IMAD.HI (FMA-heavy pipe) instead of SHF (ALU pipe);
+    // both pipes are close to full in the impulse loop (profiles/), the variants were timed on B200 and the fastest kept
+#ifndef SCN_PCG_VARIANT
+#define SCN_PCG_VARIANT 0
+#endif
+#if SCN_PCG_VARIANT == 0
+    uint32_t xs = __funnelshift_r(lo, hi, 27) ^ (hi >> 13);
+    return __funnelshift_r(xs, xs, hi >> 27);
+#elif SCN_PCG_VARIANT == 1
+    uint32_t xs = __funnelshift_r(lo, hi, 27) ^ (hi >> 13);
+    return __funnelshift_r(xs, xs, __umulhi(hi, 1u << 5));
+#else
     uint32_t xs = __funnelshift_r(lo, hi, 27) ^ __umulhi(hi, 1u << 19);
     return __funnelshift_r(xs, xs, __umulhi(hi, 1u << 5));
+#endif
 }
 __device__ __forceinline__ float ex2_approx(float x) { float y; asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
+
+// PCG32 state after j transitions from the 32-bit seed x (hi word 0): s_j = A_j x + C_j (mod 2^64) with A_j = M^j and
+// C_j = (M^j - 1) / (M - 1), compile-time constants.  Because x has no high word this is IMAD.WIDE + one IMAD per draw instead of
+// IMAD.WIDE + 2 IMAD for a chained step, and the draws of a cell no longer depend on each other.
+template <int J> struct LcgJump { static constexpr uint64_t A = LcgJump<J - 1>::A * PCG_MULT, C = LcgJump<J - 1>::C * PCG_MULT + 1ULL; };
+template <> struct LcgJump<0> { static constexpr uint64_t A = 1ULL, C = 0ULL; };
+template <int J>
+__device__ __forceinline__ uint32_t pcg_draw_at(uint32_t x) {
+    const uint64_t w = (uint64_t)x * (uint32_t)LcgJump<J>::A + LcgJump<J>::C;
+    return pcg_out((uint32_t)w, (uint32_t)(w >> 32) + x * (uint32_t)(LcgJump<J>::A >> 32));
+}
+
+// impulse K of a cell seeded with x = h + 1 (draws 2 + 4K .. 5 + 4K of the stream: set_state discards two), accumulated
+template <bool ISO_A, int K, int NIMP>
+struct ImpulseUnrolled {
+    static __device__ __forceinline__ void run(uint32_t x, float cx, float cy, float cz, float a0, float a1, float a2, float &sv, float &s0, float &s1, float &s2) {
+        const float uz = u32_to_unit(pcg_draw_at<2 + 4 * K>(x)), uy = u32_to_unit(pcg_draw_at<3 + 4 * K>(x)), ux = u32_to_unit(pcg_draw_at<4 + 4 * K>(x));
+        const uint32_t rs = pcg_draw_at<5 + 4 * K>(x);
+        const float tz = xsub(cz, uz), ty = xsub(cy, uy), tx = xsub(cx, ux);
+        const float l2 = xadd(xadd(xmul(tx, tx), xmul(ty, ty)), xmul(tz, tz));
+        const float arg = ISO_A ? -a0 * l2 : -(a0 * tx * tx + (a1 * ty * ty + a2 * tz * tz));
+        float f = ex2_approx(arg);
+        f = __uint_as_float(__float_as_uint(f) ^ (~rs & 0x80000000u));
+        f = l2 < 1.0f ? f : 0.0f;
+        sv += f; s0 = fmaf(f, tx, s0); s1 = fmaf(f, ty, s1); s2 = fmaf(f, tz, s2);
+        ImpulseUnrolled<ISO_A, K + 1, NIMP>::run(x, cx, cy, cz, a0, a1, a2, sv, s0, s1, s2);
+    }
+};
+template <bool ISO_A, int NIMP>
+struct ImpulseUnrolled<ISO_A, NIMP, NIMP> {
+    static __device__ __forceinline__ void run(uint32_t, float, float, float, float, float, float, float &, float &, float &, float &) {}
+};
 
 // All N impulses of one cell (cell3D, SCN:375-395) against the point whose cell-local coordinates are (cx, cy, cz).
 // ISO_A: the kernel's inverse covariance is a multiple of the identity in the sampling space (a0 only).
@@ -55,6 +102,9 @@ __device__ __forceinline__ float ex2_approx(float x) { float y; asm("ex2.approx.
 template <bool ISO_A, int NIMP>
 __device__ __forceinline__ void cell_accumulate(uint32_t h, uint32_t nimp_dyn, uint64_t inc, float cx, float cy, float cz, float a0, float a1, float a2,
                                                 float &sv, float &s0, float &s1, float &s2) {
+#if SCN_LCG_JUMP
+    if (NIMP > 0) { ImpulseUnrolled<ISO_A, 0, (NIMP > 0 ? NIMP : 0)>::run(h + 1u, cx, cy, cz, a0, a1, a2, sv, s0, s1, s2); return; }
+#endif
     // set_state(h + 1u) (the +1 wraps in 32 bits), then two discarded draws (sampling/UniformSampler.hpp:71-75)
     uint32_t lo = h + 1u, hi = 0u;
     lcg_step(lo, hi, inc); lcg_step(lo, hi, inc);

@@ -1,10 +1,10 @@
 set -x; mkdir -p gpurun_out
-N=${NG:-2}
-TR="python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29511"
-timeout 600 python bench.py --steps 3 --warmup 3 > gpurun_out/bench_n1.json 2> gpurun_out/bench_n1.err; tail -2 gpurun_out/bench_n1.err
-timeout 600 $TR bench.py --gpus $N --steps 3 --warmup 3 > gpurun_out/bench_n$N.json 2> gpurun_out/bench_n$N.err; tail -3 gpurun_out/bench_n$N.err
-timeout 600 python tools/render.py --config c1 --res 1024 --spp 16 > gpurun_out/render_scale.log 2>&1
-timeout 600 $TR tools/render.py --config c1 --res 1024 --spp 16 >> gpurun_out/render_scale.log 2>&1
-timeout 600 python tools/render.py --config c5 --res 1024 --spp 16 >> gpurun_out/render_scale.log 2>&1
-timeout 600 $TR tools/render.py --config c5 --res 1024 --spp 16 >> gpurun_out/render_scale.log 2>&1
-grep workload gpurun_out/render_scale.log
+python -m pytest tests -m gpu -q -k "microbench or golden" 2>&1 | tail -2
+SCN_LIB_PATH=$PWD/sparse_conv_gpis_tungsten_b200/libscn_var0.so python bench.py --steps 3 --warmup 3 > gpurun_out/bench_var0.json 2>gpurun_out/bench_var0.err
+python bench.py --steps 3 --warmup 3 > gpurun_out/bench_var2.json 2>gpurun_out/bench_var2.err
+python - <<'PY'
+import json
+for v in (0,2):
+    d=json.loads([l for l in open('gpurun_out/bench_var%d.json'%v) if l.startswith('{')][-1])
+    print(v, round(d['value']/1e9,3), {k:round(x['evals_per_s']/1e9,3) for k,x in d['extra']['sweep'].items() if k in ('iso_N1','iso_N2','iso_N4','iso_N8','world_N1','world_N4')}, d['extra']['parity_vs_cpu_max_rel_err'])
+PY
