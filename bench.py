@@ -251,8 +251,14 @@ def run_gpu(args):
     fp32_peak = sms * 128 * 2 * f_mhz * 1e6
     ach_issue = per_gpu * w_issue(DENSITY)
     hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
+    traffic = None  # dram__bytes_read.sum + dram__bytes_write.sum of one launch from the committed ncu --set full capture, scaled to this launch size
+    try:
+        tj = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))["k_fast_noise3d<ISO=%d, NIMP=%d>" % (int(ISO), DENSITY)]
+        traffic = (tj["dram_bytes_read"] + tj["dram_bytes_write"]) * (n / tj["evals_per_launch"])
+    except Exception:
+        pass
     roofline = {"bound": "fp32-issue", "achieved": ach_issue / 1e12, "peak": issue_peak / 1e12, "unit": "Tlane-op/s", "frac": ach_issue / issue_peak,
-                "traffic": None, "kernel": "k_fast_noise3d<ISO=%d, NIMP=%d>" % (int(ISO), DENSITY), "avg_launch_ms": ms_max / args.steps,
+                "traffic": traffic, "traffic_unit": "bytes per launch (ncu dram read+write; algorithmic = 40 B x evals_per_launch)", "kernel": "k_fast_noise3d<ISO=%d, NIMP=%d>" % (int(ISO), DENSITY), "avg_launch_ms": ms_max / args.steps,
                 "algorithmic": {"lane_ops_per_eval": w_issue(DENSITY), "flops_per_eval": w_flop(DENSITY), "bytes_per_eval": 40, "evals_per_launch": n},
                 "fp32_flops": {"achieved": per_gpu * w_flop(DENSITY) / 1e12, "peak": fp32_peak / 1e12, "unit": "TFLOP/s", "frac": per_gpu * w_flop(DENSITY) / fp32_peak},
                 "hbm": {"achieved": per_gpu * 40 / 1e9, "peak": hbm_peak, "unit": "GB/s", "frac": per_gpu * 40 / 1e9 / hbm_peak,
