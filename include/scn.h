@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define SCN_ABI_VERSION 1
+#define SCN_ABI_VERSION 2
 
 /* error codes */
 #define SCN_OK 0
@@ -53,6 +53,12 @@ extern "C" {
 /* CovarianceFunctionFactory strings, math/GaussianProcessFactory.cpp:25-38 (covered subset) */
 #define SCN_COV_SQUARED_EXPONENTIAL 0
 #define SCN_COV_PROC_NONSTATIONARY 1 /* "proc_nonstationary" wrapping a squared_exponential "cov" */
+/* alternative splat kernels (math/GPFunctions.cpp:1020-1082, 1127-1214).  They have no second derivative, no 1D family and
+ * never initialise the world<->isotropic transforms, so the reference only defines them for world-space 3D sampling
+ * without Renewal conditioning; scn_medium_create answers SCN_EUNSUPPORTED for anything else. */
+#define SCN_COV_MATERN 2             /* "matern": "sigma" "v" (0.5 | 1.5 | 2.5) "lengthScale" "aniso" "localScale" */
+#define SCN_COV_GABOR_ANISO 3        /* "gabor_aniso": "sigma" "a_inv" "f_inv" "omega" "localScale"               */
+#define SCN_COV_GABOR_ISO 4          /* "gabor_iso": "sigma" "a_inv" "f_inv" "localScale"                         */
 
 /* ProceduralScalar / ProceduralVector, math/GPFunctions.hpp:407-427,604-692,693-781 */
 #define SCN_FIELD_NONE 0
@@ -124,6 +130,11 @@ typedef struct scn_medium_desc {
     int32_t multires;                 /* "multiResolutionGrid"     default false      */
     scn_field_desc ls;                /* "ls"  (vector field; lateral scale)          */
     scn_field_desc var;               /* "var" (scalar field; variance)               */
+    /* matern / gabor (appended in ABI version 2) */
+    float matern_v;                   /* "v"                       default 1          */
+    float gabor_a_inv;                /* "a_inv"                   default 1          */
+    float gabor_f_inv;                /* "f_inv"                   default 1          */
+    float gabor_omega[3];             /* "omega" (normalised at parse time; the reference leaves it uninitialised when absent) */
 } scn_medium_desc;
 
 typedef struct scn_medium scn_medium; /* opaque; replaces the SparseConvolutionNoiseMedium object */

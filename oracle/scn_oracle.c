@@ -138,6 +138,8 @@ struct orc_medium {
     float ls_max;            /* sparseConvNoiseMaxLateralScale, GPF:1729-1733 */
     float sigma_s_over_t;
     int absorption_only;
+    int kernel;              /* SCN_COV_SQUARED_EXPONENTIAL | SCN_COV_MATERN | SCN_COV_GABOR_ANISO | SCN_COV_GABOR_ISO */
+    float k_a, k_f; v3 k_omega; /* Gabor: _a, _f, _omega (GPF:1087-1097) */
 };
 
 orc_medium *orc_medium_create(const scn_medium_desc *desc) {
@@ -146,7 +148,15 @@ orc_medium *orc_medium_create(const scn_medium_desc *desc) {
     orc_medium *m = (orc_medium *)calloc(1, sizeof *m);
     m->d = *desc;
     m->n_imp = (uint32_t)desc->impulse_density;
-    m->stationary = desc->cov_type == SCN_COV_SQUARED_EXPONENTIAL;
+    m->stationary = desc->cov_type != SCN_COV_PROC_NONSTATIONARY;
+    m->kernel = desc->cov_type >= SCN_COV_MATERN ? desc->cov_type : SCN_COV_SQUARED_EXPONENTIAL;
+    if (m->kernel != SCN_COV_SQUARED_EXPONENTIAL) {
+        /* GPF:870-880, 1087-1097, 1156-1163: no second derivative, no 1D family, transforms never initialised */
+        int cond = !desc->single_realization && (desc->correlation_context == SCN_CTX_RENEWAL || desc->correlation_context == SCN_CTX_RENEWAL_PLUS);
+        if (desc->sampling_1d || desc->isotropic_3d_sampling || cond) { snprintf(g_err, sizeof g_err, "matern / gabor: world-space 3D sampling without conditioning only"); free(m); return NULL; }
+        m->k_a = (float)(1.0 / desc->gabor_a_inv); m->k_f = (float)(1.0 / desc->gabor_f_inv);
+        m->k_omega = V3(desc->gabor_omega[0], desc->gabor_omega[1], desc->gabor_omega[2]);
+    }
     m->multires = !m->stationary && desc->multires;
     m->l_conv = desc->length_scale * sqrtf(2.f) / 2;
     m->l_aniso = V3(m->l_conv * desc->aniso[0], m->l_conv * desc->aniso[1], m->l_conv * desc->aniso[2]);
@@ -221,9 +231,68 @@ static float cov_amplitude(const orc_medium *m, v3 p) {
 static float cov_radius(const orc_medium *m, int is_identity, float local_scale) {
     if (!m->stationary) { local_scale *= m->multires ? 1.0 : m->ls_max; local_scale *= 1.f; }
     float sf = m->d.kernel_scale;
+    if (m->kernel == SCN_COV_MATERN) { /* GPF:1020-1025 */
+        if (is_identity) return sf;
+        float v[3], mf = 0.f;
+        for (int i = 0; i < 3; ++i) { v[i] = m->d.length_scale / sqrtf(m->d.aniso[i]); if (isinf(v[i]) || isnan(v[i])) v[i] = 0.f; }
+        mf = max3f(v[0], v[1], v[2]);
+        return (float)(sf * local_scale * sqrt(2) / 2 * mf);
+    }
+    if (m->kernel == SCN_COV_GABOR_ANISO) return (float)(sf * sqrt(2) / 2 * 1.0 / m->k_a); /* GPF:1127-1130 */
+    if (m->kernel == SCN_COV_GABOR_ISO) return (float)(sf * sqrt(2) / 4 * 1.0 / m->k_a);   /* GPF:1185-1188 */
     if (is_identity) return sf;
     float mf = max3f(m->l_aniso.x, m->l_aniso.y, m->l_aniso.z);
     return sf * local_scale * mf;
+}
+/* Matern / Gabor sparseConvNoiseVariance3D (GPF:1029-1044, 1134-1138, 1192-1196) */
+static float alt_variance3d(const orc_medium *m, float density, float R) {
+    double per_unit = density / (R * R * R), integral;
+    if (m->kernel == SCN_COV_MATERN) {
+        float l = m->d.length_scale, v = m->d.matern_v;
+        if (v == 0.5f) integral = 2.0 * M_PI * l;
+        else if (v == 1.5f) integral = pow(M_PI * l, 3) / (24 * sqrt(3));
+        else if (v == 2.5f) integral = M_PI * pow(l, 3) / (5 * sqrt(5));
+        else return 0.f;
+    } else if (m->kernel == SCN_COV_GABOR_ANISO) integral = pow(1.0 / m->k_a, 3) * (1 + exp(-2.0 * M_PI * sqrf(m->k_f / m->k_a))) / (4 * sqrt(2));
+    else integral = 2 * sqrt(2) * M_PI * sqrf(m->k_f) / m->k_a * (1 - exp(-2 * M_PI * m->k_f / sqrf(m->k_a)));
+    return (float)(per_unit * integral);
+}
+/* modified Bessel function of the second kind K_n(x), n = 0, 1 (the reference calls boost::math::cyl_bessel_k): trapezoid rule on
+ * K_n(x) = int_0^inf exp(-x cosh t) cosh(n t) dt, which converges geometrically for this integrand */
+static double bessel_k(int n, double x) {
+    const double h = 0.125;
+    double sum = 0.5 * exp(-x);
+    for (int i = 1; i < 4096; ++i) {
+        double t = i * h, e = x * cosh(t);
+        if (e > 745.) break;
+        sum += exp(-e) * (n ? cosh(t) : 1.0);
+    }
+    return sum * h;
+}
+/* splattingKernel3DVal / 1stGrad of MaternCovariance (GPF:1046-1082), GaborAnisotropicCovariance (GPF:1142-1153) and
+ * GaborIsotropicCovariance (GPF:1200-1214); isCov, isIsotropic and the scales are ignored by these classes */
+static v4 alt_kernel3d(const orc_medium *m, v3 ab) {
+    if (m->kernel == SCN_COV_MATERN) {
+        double abLen = v3_len(ab); float l = m->d.length_scale, v = m->d.matern_v, val, gk;
+        if (v == 0.5f) { val = (float)(exp(-abLen / l) / abLen); gk = -(float)(exp(-abLen / l) * (1 / pow(abLen, 3) - 1 / (pow(abLen, 2) * l))); }
+        else if (v == 1.5f) { double rs = sqrt(3.) * abLen / l; val = (float)bessel_k(0, rs); gk = -(float)(bessel_k(1, rs) * sqrt(3.) / l / abLen); }
+        else { val = (float)exp(-sqrt(5.) * abLen / l); gk = -(float)(exp(-sqrt(5.) * abLen / l) * sqrt(5.) / l / abLen); }
+        return V4(val, gk * ab.x, gk * ab.y, gk * ab.z);
+    }
+    float a = m->k_a, f = m->k_f;
+    if (m->kernel == SCN_COV_GABOR_ANISO) {
+        float od = v3_dot(m->k_omega, ab);
+        float val = (float)(exp(-M_PI * sqrf(a) * v3_lensq(ab)) * cos(2.f * M_PI * f * od));
+        float A = (float)exp(-M_PI * sqrf(a) * v3_lensq(ab)), B = (float)cos(2.f * M_PI * f * od);
+        float g1 = -(float)(A * sin(2.f * M_PI * f * od) * 2.f * M_PI * f), g2 = (float)(B * A * 2.f * M_PI * sqrf(a));
+        v3 g = v3_sub(v3_scale(m->k_omega, g1), v3_scale(ab, g2));
+        return V4(val, g.x, g.y, g.z);
+    }
+    float r = v3_len(ab);
+    float val = (float)(exp(-M_PI * sqrf(a * r)) * 2 * f / r * sin(2 * M_PI * f * r));
+    float gk = (float)(2 * f * exp(-M_PI * sqrf(a) * v3_lensq(ab)) *
+                       (-sin(2 * M_PI * f * r) / pow(r, 3) - 2 * M_PI * sqrf(a) * sin(2 * M_PI * f * r) / r + 2 * M_PI * f * cos(2 * M_PI * f * r) / sqrf(r)));
+    return V4(val, gk * ab.x, gk * ab.y, gk * ab.z);
 }
 /* SquaredExponentialCovariance::sparseConvNoiseVariance3D/1D (GPF:741-760) */
 static float se_variance3d(const orc_medium *m, float density, float R, int is_identity, float global_scale, float local_scale) {
@@ -237,7 +306,9 @@ static float se_variance3d(const orc_medium *m, float density, float R, int is_i
 static float se_variance1d(float density, float R, float local_scale) {
     double per_unit = density / R; double integral = sqrt(M_PI) * local_scale; return (float)(per_unit * integral);
 }
+static float alt_variance3d(const orc_medium *m, float density, float R);
 static float cov_variance3d(const orc_medium *m, v3 p, float density, float R, int is_identity, float global_scale) { /* GPF:615-617, 1251-1254 */
+    if (m->kernel != SCN_COV_SQUARED_EXPONENTIAL) return alt_variance3d(m, density, R);
     if (m->stationary) return se_variance3d(m, density, R, is_identity, global_scale, 1.0f);
     float ls = m->multires ? 1.0f : cov_ns_scale(m, p);
     return se_variance3d(m, density, R, is_identity, global_scale, ls);
@@ -273,6 +344,7 @@ static v3 se_inv_cov_diag(const orc_medium *m, int is_cov, int is_iso, float gs,
 static v4 cov_kernel3d(const orc_medium *m, v3 pa, v3 pb, int is_cov, int is_iso, float gs, v3 p_world) {
     float ls = cov_ns_scale(m, p_world);
     v3 ab = v3_sub(pa, pb);
+    if (m->kernel != SCN_COV_SQUARED_EXPONENTIAL) return alt_kernel3d(m, ab);
     v3 M = se_inv_cov_diag(m, is_cov, is_iso, gs, ls);
     float absq = (ab.x * M.x) * ab.x + ((ab.y * M.y) * ab.y + (ab.z * M.z) * ab.z);
     float f = expf(-absq);

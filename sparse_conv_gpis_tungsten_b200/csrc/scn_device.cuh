@@ -208,6 +208,78 @@ SCN_HD f4 se_kernel3d_grad(f3 ab, f3 M, f3 c) {
     return F4((dx * f) * c.x + (dy * f) * c.y + (dz * f) * c.z,
               h00 * c.x + h01 * c.y + h02 * c.z, h01 * c.x + h11 * c.y + h12 * c.z, h02 * c.x + h12 * c.y + h22 * c.z);
 }
+// ---------------------------------------------------------------- alternative splat kernels (GPF:1046-1082, 1142-1153, 1200-1214)
+// Modified Bessel functions K0, K1 (the reference calls boost::math::cyl_bessel_k in MaternCovariance, v = 1.5): polynomial
+// approximations of Abramowitz & Stegun 9.8.1-9.8.8, |relative error| < 3e-7, evaluated in double.
+SCN_HD double bessel_i0_small(double x) { // |x| <= 3.75
+    double t = x / 3.75; t *= t;
+    return 1.0 + t * (3.5156229 + t * (3.0899424 + t * (1.2067492 + t * (0.2659732 + t * (0.0360768 + t * 0.0045813)))));
+}
+SCN_HD double bessel_i1_small(double x) {
+    double t = x / 3.75; t *= t;
+    return x * (0.5 + t * (0.87890594 + t * (0.51498869 + t * (0.15084934 + t * (0.02658733 + t * (0.00301532 + t * 0.00032411))))));
+}
+SCN_HD double bessel_k0(double x) {
+    if (x <= 2.0) {
+        double y = x * x / 4.0;
+        return -log(x / 2.0) * bessel_i0_small(x) + (-0.57721566 + y * (0.42278420 + y * (0.23069756 + y * (0.03488590 + y * (0.00262698 + y * (0.00010750 + y * 0.0000074))))));
+    }
+    double y = 2.0 / x;
+    return exp(-x) / sqrt(x) * (1.25331414 + y * (-0.07832358 + y * (0.02189568 + y * (-0.01062446 + y * (0.00587872 + y * (-0.00251540 + y * 0.00053208))))));
+}
+SCN_HD double bessel_k1(double x) {
+    if (x <= 2.0) {
+        double y = x * x / 4.0;
+        return log(x / 2.0) * bessel_i1_small(x) + (1.0 / x) * (1.0 + y * (0.15443144 + y * (-0.67278579 + y * (-0.18156897 + y * (-0.01919402 + y * (-0.00110404 + y * -0.00004686))))));
+    }
+    double y = 2.0 / x;
+    return exp(-x) / sqrt(x) * (1.25331414 + y * (0.23498619 + y * (-0.03655620 + y * (0.01504268 + y * (-0.00780353 + y * (0.00325614 + y * -0.00068245))))));
+}
+// splattingKernel3D for "matern" / "gabor_aniso" / "gabor_iso": value + first gradient for ab = pa - pb.  The reference evaluates
+// these in double and rounds each factor to float where it casts; isCov / isIsotropic / scales are ignored by these classes.
+SCN_FN f4 alt_kernel3d(const Params &P, f3 ab) {
+    const float lsq = xadd(xadd(xmul(ab.x, ab.x), xmul(ab.y, ab.y)), xmul(ab.z, ab.z));
+    const float rf = xsqrt(lsq);
+    if (P.kernel == SCN_COV_MATERN) { // GPF:1046-1082
+        const double r = (double)rf, l = (double)P.k_l;
+        float val, gk;
+        if (P.k_v == 0.5f) {
+            double e = exp(-r / l);
+            val = (float)(e / r);
+            gk = -(float)(e * (1.0 / (r * r * r) - 1.0 / (r * r * l))); // sic: the reference's sign between the two terms
+        } else if (P.k_v == 1.5f) {
+            double rs = 1.7320508075688772 * r / l;
+            val = (float)bessel_k0(rs);
+            gk = -(float)(bessel_k1(rs) * 1.7320508075688772 / l / r);
+        } else {
+            double e = exp(-2.23606797749979 * r / l);
+            val = (float)e;
+            gk = -(float)(e * 2.23606797749979 / l / r);
+        }
+        return F4(val, gk * ab.x, gk * ab.y, gk * ab.z);
+    }
+    const double PI_D = 3.14159265358979323846;
+    const float a = P.k_a, f = P.k_f;
+    if (P.kernel == SCN_COV_GABOR_ANISO) { // GPF:1142-1153
+        const float od = xadd(xadd(xmul(P.k_omega[0], ab.x), xmul(P.k_omega[1], ab.y)), xmul(P.k_omega[2], ab.z));
+        const double ph = 2.0 * PI_D * (double)f * (double)od;
+        const double env = exp(-PI_D * (double)(a * a) * (double)lsq);
+        const float A = (float)env, B = (float)cos(ph);
+        const float val = (float)(env * cos(ph));
+        const float g1 = -(float)((double)A * sin(ph) * 2.0 * PI_D * (double)f);
+        const float g2 = (float)((double)B * (double)A * 2.0 * PI_D * (double)(a * a));
+        return F4(val, g1 * P.k_omega[0] - g2 * ab.x, g1 * P.k_omega[1] - g2 * ab.y, g1 * P.k_omega[2] - g2 * ab.z);
+    }
+    // gabor_iso, GPF:1200-1214
+    const double r = (double)rf;
+    const double ph = 2.0 * PI_D * (double)f * r;
+    const float ar = a * rf;
+    const float val = (float)(exp(-PI_D * (double)(ar * ar)) * 2.0 * (double)f / r * sin(ph));
+    const double a2 = (double)(a * a);
+    const float gk = (float)(2.0 * (double)f * exp(-PI_D * a2 * (double)lsq) *
+                             (-sin(ph) / (r * r * r) - 2.0 * PI_D * a2 * sin(ph) / r + 2.0 * PI_D * (double)f * cos(ph) / (double)(rf * rf)));
+    return F4(val, gk * ab.x, gk * ab.y, gk * ab.z);
+}
 // 1D kernels (GPF:835-865)
 SCN_HD float se_k1d_val(float ab, float ls) { float den = 2.0f * ls * ls; return fast_exp(-(ab * ab / den)); }
 SCN_HD float se_k1d_grad(float ab, float ls) { float den = 2.0f * ls * ls; return -2.0f * ab / den * se_k1d_val(ab, ls); }
@@ -303,7 +375,7 @@ SCN_FN f4 noise3d(const Params &P, f3 p, uint32_t seed, float R, f3 M) {
                     if (l2 < 1.0f) {
                         // kernel(R*p, R*p_i): ab = R*p - R*p_i (SCN:390)
                         f3 ab = F3(xsub(xmul(R, cx), xmul(R, px)), xsub(xmul(R, cy), xmul(R, py)), xsub(xmul(R, cz), xmul(R, pz)));
-                        f4 kv = se_kernel3d(ab, M);
+                        f4 kv = P.kernel == SCN_COV_SQUARED_EXPONENTIAL ? se_kernel3d(ab, M) : alt_kernel3d(P, ab);
                         float w = ws < 0.5f ? -1.f : 1.f;
                         cs.x += w * kv.x; cs.y += w * kv.y; cs.z += w * kv.z; cs.w += w * kv.w;
                     }

@@ -61,7 +61,11 @@ struct Params {
     scn_mean_desc mean, mean_add;
     FieldK ls, var;
     float log_base;            // logf(2.5f) from the host libm
-    int32_t _pad2;
+    // alternative stationary splat kernels (math/GPFunctions.cpp:1020-1082, 1127-1214): world-space sampling only
+    int32_t kernel;            // SCN_COV_SQUARED_EXPONENTIAL | SCN_COV_MATERN | SCN_COV_GABOR_ANISO | SCN_COV_GABOR_ISO
+    float k_v, k_l;            // Matern: _v, _l
+    float k_a, k_f;            // Gabor: _a = 1 / a_inv, _f = 1 / f_inv (float members assigned from double quotients)
+    float k_omega[3];          // Gabor anisotropic: normalised _omega
 };
 
 int params_from_desc(const scn_medium_desc &d, Params &p);

@@ -162,16 +162,34 @@ int parseField(const JVal &j, scn_field_desc &f, bool vector) {
     return SCN_OK;
 }
 
-int parseSE(const JVal &j, scn_medium_desc &d) {
+int parseSE(const JVal &j, scn_medium_desc &d, bool allowAlt) {
     std::string type;
     if (!getS(j, "type", type)) return set_error(SCN_EJSON, "covariance: missing \"type\"");
+    getF(j, "localScale", d.kernel_scale); // StationaryCovariance::fromJson, math/GPFunctions.hpp:1481-1484
+    if (allowAlt && (type == "matern" || type == "gabor_aniso" || type == "gabor_iso")) {
+        getF(j, "sigma", d.sigma);
+        if (type == "matern") { // math/GPFunctions.cpp:870-880
+            d.cov_type = SCN_COV_MATERN;
+            getF(j, "v", d.matern_v); getF(j, "lengthScale", d.length_scale); getVec3(j, "aniso", d.aniso);
+            return SCN_OK;
+        }
+        d.cov_type = type == "gabor_aniso" ? SCN_COV_GABOR_ANISO : SCN_COV_GABOR_ISO; // math/GPFunctions.cpp:1087-1097, 1156-1163
+        getF(j, "a_inv", d.gabor_a_inv); getF(j, "f_inv", d.gabor_f_inv);
+        if (d.cov_type == SCN_COV_GABOR_ANISO) {
+            if (!j.get("omega")) return set_error(SCN_EINVAL, "gabor_aniso: \"omega\" is mandatory (the reference reads it uninitialised when absent)");
+            getVec3(j, "omega", d.gabor_omega);
+            float *o = d.gabor_omega; // Vec3f::normalize(): multiply by the reciprocal length (math/Vec.hpp)
+            float len = std::sqrt(o[0] * o[0] + o[1] * o[1] + o[2] * o[2]), inv = 1.0f / len;
+            o[0] *= inv; o[1] *= inv; o[2] *= inv;
+        }
+        return SCN_OK;
+    }
     if (type != "squared_exponential") {
         static const char *known[] = {"rational_quadratic", "matern", "gabor_aniso", "gabor_iso", "dot_product", "periodic", "thin_plate",
                                       "grid_nonstationary", "mg_nonstationary", "neural_nonstationary", "proc_nonstationary"};
-        for (const char *k : known) if (type == k) return set_error(SCN_EUNSUPPORTED, "covariance '%s' is not covered (squared_exponential and proc_nonstationary over it are)", type.c_str());
+        for (const char *k : known) if (type == k) return set_error(SCN_EUNSUPPORTED, "covariance '%s' is not covered here (squared_exponential, matern, gabor_aniso, gabor_iso and proc_nonstationary over squared_exponential are)", type.c_str());
         return set_error(SCN_EJSON, "Invalid covariance: '%s'", type.c_str());
     }
-    getF(j, "localScale", d.kernel_scale);
     getF(j, "sigma", d.sigma); getF(j, "lengthScale", d.length_scale); getVec3(j, "aniso", d.aniso);
     getB(j, "useAnisoMtx", d.use_aniso_mtx);
     if (d.use_aniso_mtx) return set_error(SCN_EUNSUPPORTED, "\"useAnisoMtx\" (full anisotropy matrix) is not covered");
@@ -181,11 +199,11 @@ int parseSE(const JVal &j, scn_medium_desc &d) {
 int parseCov(const JVal &j, scn_medium_desc &d) {
     std::string type;
     if (!getS(j, "type", type)) return set_error(SCN_EJSON, "covariance: missing \"type\"");
-    if (type != "proc_nonstationary") { d.cov_type = SCN_COV_SQUARED_EXPONENTIAL; return parseSE(j, d); }
+    if (type != "proc_nonstationary") { d.cov_type = SCN_COV_SQUARED_EXPONENTIAL; return parseSE(j, d, true); }
     d.cov_type = SCN_COV_PROC_NONSTATIONARY;
     const JVal *inner = j.get("cov");
     if (!inner) return set_error(SCN_EJSON, "proc_nonstationary: missing \"cov\"");
-    if (int rc = parseSE(*inner, d)) return rc;
+    if (int rc = parseSE(*inner, d, false)) return rc;
     getB(j, "multiResolutionGrid", d.multires);
     if (j.get("aniso")) return set_error(SCN_EUNSUPPORTED, "proc_nonstationary \"aniso\" (rotation-anisotropy field) is not covered");
     if (const JVal *v = j.get("var")) if (int rc = parseField(*v, d.var, false)) return rc;
@@ -246,6 +264,7 @@ int desc_default(scn_medium_desc *d) {
     d->sigma = 1.f; d->length_scale = 1.f; d->aniso[0] = d->aniso[1] = d->aniso[2] = 1.f; d->kernel_scale = 3.0f;
     d->aniso_mtx[0] = d->aniso_mtx[4] = d->aniso_mtx[8] = 1.f;
     fieldDefault(d->ls); fieldDefault(d->var);
+    d->matern_v = 1.0f; d->gabor_a_inv = 1.f; d->gabor_f_inv = 1.f; d->gabor_omega[2] = 1.f;
     return SCN_OK;
 }
 

@@ -43,7 +43,19 @@ int params_from_desc(const scn_medium_desc &d, Params &p) {
     if (d.correlation_context < SCN_CTX_GLOBAL || d.correlation_context > SCN_CTX_NONE)
         return set_error(SCN_EINVAL, "correlation_context is mandatory (media/GaussianProcessMedium.cpp:104-106)");
     if (d.use_aniso_mtx) return set_error(SCN_EUNSUPPORTED, "useAnisoMtx is not covered");
-    if (d.cov_type != SCN_COV_SQUARED_EXPONENTIAL && d.cov_type != SCN_COV_PROC_NONSTATIONARY) return set_error(SCN_EINVAL, "bad cov_type");
+    if (d.cov_type < SCN_COV_SQUARED_EXPONENTIAL || d.cov_type > SCN_COV_GABOR_ISO) return set_error(SCN_EINVAL, "bad cov_type");
+    const bool alt = d.cov_type >= SCN_COV_MATERN;
+    if (alt) {
+        // these kernels have no second derivative and no 1D family (math/GPFunctions.hpp:1336-1345,1509-1516 print "not implemented"), and
+        // their fromJson never writes _world_to_local (math/GPFunctions.cpp:870-880,1087-1097): only world-space 3D sampling without
+        // Renewal conditioning is defined behaviour in the reference
+        if (d.sampling_1d) return set_error(SCN_EUNSUPPORTED, "matern / gabor kernels have no 1D sampling in the reference");
+        if (d.isotropic_3d_sampling) return set_error(SCN_EUNSUPPORTED, "matern / gabor kernels: isotropic_3D_sampling reads uninitialised transforms in the reference; use world-space sampling");
+        if (!d.single_realization && (d.correlation_context == SCN_CTX_RENEWAL || d.correlation_context == SCN_CTX_RENEWAL_PLUS))
+            return set_error(SCN_EUNSUPPORTED, "matern / gabor kernels have no second derivative: renewal / renewal+ conditioning is not defined for them");
+        if (d.cov_type == SCN_COV_MATERN && d.matern_v != 0.5f && d.matern_v != 1.5f && d.matern_v != 2.5f)
+            return set_error(SCN_EINVAL, "Matern kernel only implemented for v = 0.5, 1.5, 2.5");
+    }
     if (d.mean.type < SCN_MEAN_HOMOGENEOUS || d.mean.type > SCN_MEAN_LINEAR) return set_error(SCN_EINVAL, "bad mean type");
     if (!(d.impulse_density >= 0.f) || d.impulse_density > 4096.f) return set_error(SCN_EINVAL, "impulse_density out of range");
     if (d.min_step == 0) return set_error(SCN_EINVAL, "min_step must be positive");
@@ -52,7 +64,11 @@ int params_from_desc(const scn_medium_desc &d, Params &p) {
     p.ctx = d.correlation_context; p.corr_xy = d.correlation_xy;
     p.activate_conditioning = !d.single_realization && (d.correlation_context == SCN_CTX_RENEWAL || d.correlation_context == SCN_CTX_RENEWAL_PLUS);
     p.scheme = (!d.single_realization && d.sampling_1d) ? d.sampling_scheme_1d : SCN_SCHEME_UNI;
-    p.stationary = d.cov_type == SCN_COV_SQUARED_EXPONENTIAL;
+    p.stationary = d.cov_type != SCN_COV_PROC_NONSTATIONARY;
+    p.kernel = alt ? d.cov_type : SCN_COV_SQUARED_EXPONENTIAL;
+    p.k_v = d.matern_v; p.k_l = d.length_scale;
+    p.k_a = (float)(1.0 / d.gabor_a_inv); p.k_f = (float)(1.0 / d.gabor_f_inv); // GPF:1090-1093
+    for (int i = 0; i < 3; ++i) p.k_omega[i] = d.gabor_omega[i];
     p.multires = !p.stationary && d.multires;
     p.surf_vol_sep = d.surf_vol_phase_separate; p.surf_vol_thresh = d.surf_vol_phase_amp_thresh;
     p.step_size = d.step_size; p.min_step = d.min_step; p.max_bounces = d.max_bounces;
@@ -93,6 +109,29 @@ int params_from_desc(const scn_medium_desc &d, Params &p) {
         p.lvl_add_seed[i] = (int)std::floor(std::log(s) / std::log(2.5f));
         p.lvl_R_world[i] = d.kernel_scale * s * p.l_aniso_max;
         p.lvl_nf_world[i] = std::sqrt(host_se_variance3d(p, p.lvl_R_world[i], false, s, 1.0f));
+    }
+    if (alt) {
+        // splattingKernelRadius(false, 1.0) and sparseConvNoiseVariance3D of the alternative kernels, same float/double promotions
+        const float sf = d.kernel_scale;
+        double integral = 0.;
+        if (d.cov_type == SCN_COV_MATERN) { // GPF:1020-1044
+            float m = 0.f;
+            for (int i = 0; i < 3; ++i) { float v = d.length_scale / std::sqrt(d.aniso[i]); if (std::isinf(v) || std::isnan(v)) v = 0.f; m = std::fmax(m, v); }
+            p.R_world = (float)(sf * 1.0f * std::sqrt(2) / 2 * m);
+            const float l = d.length_scale;
+            if (d.matern_v == 0.5f) integral = 2.0 * M_PI * l;
+            else if (d.matern_v == 1.5f) integral = std::pow(M_PI * l, 3) / (24 * std::sqrt(3));
+            else integral = M_PI * std::pow(l, 3) / (5 * std::sqrt(5));
+        } else if (d.cov_type == SCN_COV_GABOR_ANISO) { // GPF:1127-1140
+            p.R_world = (float)(sf * std::sqrt(2) / 2 * 1.0 / p.k_a);
+            float q = p.k_f / p.k_a; q = q * q;
+            integral = std::pow(1.0 / p.k_a, 3) * (1 + std::exp(-2.0 * M_PI * q)) / (4 * std::sqrt(2));
+        } else { // GPF:1185-1198
+            p.R_world = (float)(sf * std::sqrt(2) / 4 * 1.0 / p.k_a);
+            integral = 2 * std::sqrt(2) * M_PI * (p.k_f * p.k_f) / p.k_a * (1 - std::exp(-2 * M_PI * p.k_f / (p.k_a * p.k_a)));
+        }
+        double per_unit = p.density / (p.R_world * p.R_world * p.R_world);
+        p.nf_world = std::sqrt((float)(per_unit * integral));
     }
     p.gp_id = d.gp_id; p.has_mean_add = d.has_mean_additional; p.id_add = d.id_additional;
     p.mean = d.mean; p.mean_add = d.mean_additional;

@@ -16,6 +16,8 @@ NE, NR = 192, 96
 
 def main():
     info = open(os.path.join(S.ORACLE_DIR, "_ref", "BUILDINFO.txt")).read().strip()
+    if "--only-missing" in sys.argv:
+        return media(info)
     prim = S.CpuImpl("ref", S.MEDIA["c1_sphere_3d_none"])
     L = prim.lib
     L.ref_xxhash32_1.restype = L.ref_xxhash32_2.restype = L.ref_xxhash32_3.restype = L.ref_xxhash32_4.restype = __import__("ctypes").c_uint32
@@ -39,8 +41,13 @@ def main():
     np.savez_compressed(os.path.join(S.GOLDEN_DIR, "primitives.npz"), keys=keys, h1=h1, h2=h2, h3=h3, h4=h4, seeds=seeds, streams=streams, next3d=n3,
                         box_muller=bm, levels=lv, buildinfo=info)
     prim.close()
+    media(info)
 
+
+def media(info):
     for name, mj in S.MEDIA.items():
+        if "--only-missing" in sys.argv and os.path.exists(os.path.join(S.GOLDEN_DIR, name + ".npz")):
+            continue
         ref = S.CpuImpl("ref", mj)
         g = {"medium_json": json.dumps(mj), "buildinfo": info}
         p, d = S.eval_points(NE, lo=-1.5, hi=1.5)

@@ -101,6 +101,13 @@ MEDIA = {
                                  "right": {"type": "standard", "id": 1, "mean": {"type": "spherical", "center": [0.5, 0.1, 0], "radius": 0.6},
                                            "covariance": {"type": "squared_exponential", "sigma": 0.05, "lengthScale": 0.1, "aniso": [1, 1, 1]}}}}),
     "absorption_only": medium(sigma_a=1.0, sigma_s=0.0),
+    # alternative splat kernels: world-space 3D sampling, no conditioning
+    "matern05_world": medium(isotropic_3D_sampling=False, covariance={"type": "matern", "sigma": 0.05, "v": 0.5, "lengthScale": 0.1, "aniso": [1, 1, 1]}),
+    "matern15_world": medium(isotropic_3D_sampling=False, impulse_density=4, covariance={"type": "matern", "sigma": 0.05, "v": 1.5, "lengthScale": 0.12, "aniso": [1, 0.6, 1.5], "localScale": 2.5}),
+    "matern25_world_global": medium(isotropic_3D_sampling=False, correlation_context="global", single_realization=False,
+                                    covariance={"type": "matern", "sigma": 0.05, "v": 2.5, "lengthScale": 0.1, "aniso": [1, 1, 1]}),
+    "gabor_aniso_world": medium(isotropic_3D_sampling=False, covariance={"type": "gabor_aniso", "sigma": 0.05, "a_inv": 0.15, "f_inv": 0.2, "omega": [1, 2, 0.5]}),
+    "gabor_iso_world": medium(isotropic_3D_sampling=False, impulse_density=5, covariance={"type": "gabor_iso", "sigma": 0.05, "a_inv": 0.15, "f_inv": 0.25, "localScale": 3.5}),
 }
 IS_1D = {k: bool(v.get("1D_sampling")) for k, v in MEDIA.items()}
 

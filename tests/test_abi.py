@@ -18,7 +18,7 @@ def test_header_symbols_exported(built_library):
     assert declared == set(abi.SYMBOLS), declared ^ set(abi.SYMBOLS)
     for name in declared:
         assert hasattr(built_library, name)
-    assert built_library.scn_abi_version() == 1
+    assert built_library.scn_abi_version() == 2
 
 
 def test_desc_layout_and_defaults(built_library):
@@ -66,10 +66,19 @@ def test_missing_correlation_context_is_an_error():
 
 
 def test_unsupported_configurations_are_refused_not_approximated():
-    mj = S.medium(covariance={"type": "matern", "sigma": 1, "lengthScale": 1, "v": 1.5})
+    mj = S.medium(covariance={"type": "rational_quadratic", "sigma": 1, "lengthScale": 1, "a": 1.5})
     with pytest.raises(abi.ScnError) as e:
         Medium.desc_from_json(mj)
     assert e.value.code == abi.SCN_EUNSUPPORTED
+    # matern / gabor: the reference defines them for world-space 3D sampling without conditioning only (GPF.cpp:870-880, GPF.hpp:1336-1345)
+    for patch in ({"isotropic_3D_sampling": True}, {"1D_sampling": True}, {"correlation_context": "renewal+", "single_realization": False}):
+        mj = S.medium(isotropic_3D_sampling=False, covariance={"type": "matern", "sigma": 1, "lengthScale": 1, "v": 1.5}); mj.update(patch)
+        with pytest.raises(abi.ScnError) as e:
+            Medium.from_json(mj)
+        assert e.value.code == abi.SCN_EUNSUPPORTED, patch
+    with pytest.raises(abi.ScnError) as e:
+        Medium.from_json(S.medium(isotropic_3D_sampling=False, covariance={"type": "matern", "v": 2.0}))
+    assert e.value.code == abi.SCN_EINVAL
     mj = S.medium(covariance={"type": "squared_exponential", "useAnisoMtx": True})
     with pytest.raises(abi.ScnError) as e:
         Medium.desc_from_json(mj)
