@@ -102,6 +102,26 @@ def time_cpu(impl, p, d, repeats=1):
     return best
 
 
+def cpu_reference_render(scene, threads):
+    """Times the unmodified reference renderer (oracle/_ref, ref_render) on `scene`; returns (camera paths / s, seconds)."""
+    import ctypes as C
+    import tempfile
+    import support as S
+    L = C.CDLL(S.REF_LIB)
+    L.ref_last_error.restype = C.c_char_p
+    res = scene["camera"]["resolution"]
+    spp = scene["renderer"]["spp"]
+    with tempfile.TemporaryDirectory() as td:
+        path = os.path.join(td, "scene.json")
+        json.dump(scene, open(path, "w"))
+        w, h, sec = C.c_int(), C.c_int(), C.c_double()
+        rgb = np.zeros((res[1], res[0], 3), np.float32)
+        rc = L.ref_render(path.encode(), threads, C.c_uint32(0xBA5EBA11), C.byref(w), C.byref(h), rgb.ctypes.data_as(C.c_void_p), C.c_size_t(rgb.size), C.byref(sec))
+        if rc != 0:
+            raise RuntimeError(L.ref_last_error().decode())
+    return res[0] * res[1] * spp / sec.value, sec.value
+
+
 def run_reference(args):
     """The reference arm: the reference's own CPU implementation of the path (oracle/_ref when it was compiled from
     /root/reference, else the oracle port), all host threads, bounded sample of the same workload per step."""
@@ -313,6 +333,16 @@ def run_gpu(args):
 
     # ---- CPU baseline on this box's host cores (bounded sample)
     threads = os.cpu_count() or 1
+    if render is not None and S.have_ref():
+        # the reference's own multithreaded renderer (Scene::load -> PathTraceIntegrator through oracle/ref_harness.cpp: ref_render) on a
+        # bounded sample of the same scene: 64x64 @4spp, all host threads
+        try:
+            ref_paths_s, ref_sec = cpu_reference_render(S.appendix_a_scene(S.MEDIA["c1_sphere_3d_none"], 64, 4), threads)
+            render["cpu_reference"] = {"camera_paths_per_s": ref_paths_s, "cores": threads, "seconds": ref_sec, "kind": "reference",
+                                       "sample": "the same scene at 64x64 @4spp through the unmodified reference renderer (NEE on, scene_bvh off)"}
+            render["speedup_vs_cpu_reference"] = render["camera_paths_per_s"] / ref_paths_s
+        except Exception as ex:  # the checker must never take the bench line down
+            render["cpu_reference"] = {"unavailable": str(ex)[:200]}
     impl, kind = cpu_impl(mj, threads)
     cs = 1 << 22
     cp, cd = host_points(cs)

@@ -20,7 +20,12 @@
 #include "sampling/PathSampleGenerator.hpp"
 #include "sampling/Gaussian.hpp"
 #include "math/Ray.hpp"
+#include "renderer/TraceableScene.hpp"
+#include "integrators/Integrator.hpp"
+#include "cameras/Camera.hpp"
+#include "thread/ThreadUtils.hpp"
 
+#include <chrono>
 #include <cstring>
 #include <functional>
 #include <memory>
@@ -333,6 +338,51 @@ int ref_nee(void *h, size_t n, const float *ray_dir, const float *normal, const 
         }
     });
     return 0;
+}
+
+// ---- the reference's own renderer (StandaloneRenderer::renderScene, src/tungsten/Shared.hpp:195-352, minus CLI and file output) ----
+// Loads a scene file through Scene::load, renders it with the scene's integrator on `threads` pool threads and copies the linear
+// framebuffer (Camera::getLinear, what Integrator::writeBuffers saves as the .pfm) into rgb (w*h*3 floats, row-major, top row first).
+// The scene must set "renderer": {"scene_bvh": false}: TraceableScene then intersects its primitives in a plain loop
+// (renderer/TraceableScene.hpp:186-193) and embree — which this recipe does not build — is never entered.
+// Returns 0, or -1 with ref_last_error() set; *w and *h are written even when rgb is too small (cap < w*h*3).
+int ref_render(const char *scene_path, int threads, uint32_t seed, int *w, int *h, float *rgb, size_t cap, double *seconds) {
+    try {
+        static bool started = false;
+        if (!started) { ThreadUtils::startThreads(threads > 0 ? threads : 1); started = true; }
+        Path path(scene_path);
+        Path dir = path.parent();
+        std::unique_ptr<Scene> scene(Scene::load(path, nullptr, &dir));
+        scene->loadResources();
+        if (scene->rendererSettings().useSceneBvh()) { g_err = "ref_render needs \"scene_bvh\": false (embree is not built)"; return -1; }
+        for (auto &m : scene->media())
+            if (auto *scn = dynamic_cast<SparseConvolutionNoiseMedium *>(m.get())) {
+                auto gp = scn->_gp->get_gaussian_process();
+                if (auto *st = dynamic_cast<StationaryCovariance *>(gp->_cov.get())) pinDiagonalTransforms(st);
+                else if (auto *ns = dynamic_cast<NonstationaryCovariance *>(gp->_cov.get())) pinDiagonalTransforms(ns->_stationaryCov.get());
+            }
+        std::unique_ptr<TraceableScene> flat(scene->makeTraceable(seed));
+        Integrator &integrator = flat->integrator();
+        auto t0 = std::chrono::steady_clock::now();
+        while (!integrator.done()) {
+            integrator.startRender([]() {});
+            integrator.waitForCompletion();
+        }
+        if (seconds) *seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+        Vec2u res = flat->cam().resolution();
+        *w = (int)res.x(); *h = (int)res.y();
+        if (!rgb || cap < (size_t)res.product() * 3) { g_err = "rgb buffer too small"; return -1; }
+        for (uint32 y = 0; y < res.y(); ++y)
+            for (uint32 x = 0; x < res.x(); ++x) {
+                Vec3f c = flat->cam().getLinear(x, y);
+                float *o = rgb + 3 * (x + (size_t)y * res.x());
+                o[0] = c.x(); o[1] = c.y(); o[2] = c.z();
+            }
+        return 0;
+    } catch (const std::exception &e) {
+        g_err = e.what();
+        return -1;
+    }
 }
 
 // Derived constants a port needs and that come out of libm on the host (multi-resolution tables etc.)

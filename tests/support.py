@@ -112,6 +112,19 @@ MEDIA = {
 IS_1D = {k: bool(v.get("1D_sampling")) for k, v in MEDIA.items()}
 
 
+def appendix_a_scene(medium_json, res, spp, max_bounces=8):
+    """SURVEY.md Appendix A.1 around `medium_json`: cube [-1.5,1.5]^3 holding the medium, constant environment, pinhole camera.
+    Box reconstruction filter (the wavefront stage's), no embree ("scene_bvh": false), no output files."""
+    return {"media": [medium_json], "bsdfs": [],
+            "primitives": [{"type": "cube", "transform": {"scale": [3, 3, 3]}, "bsdf": {"type": "forward"}, "int_medium": medium_json["name"]},
+                           {"type": "infinite_sphere", "emission": 1.0, "sample": True}],
+            "camera": {"type": "pinhole", "resolution": [res, res], "fov": 35, "tonemap": "gamma", "reconstruction_filter": "box",
+                       "transform": {"position": [0, 0, 5], "look_at": [0, 0, 0], "up": [0, 1, 0]}},
+            "integrator": {"type": "path_tracer", "min_bounces": 0, "max_bounces": max_bounces},
+            "renderer": {"spp": spp, "spp_step": spp, "adaptive_sampling": False, "stratified_sampler": False, "scene_bvh": False,
+                         "output_file": "", "hdr_output_file": "", "overwrite_output_files": True}}
+
+
 # ------------------------------------------------------------------------------------------------ seeded inputs
 def eval_points(n, seed=1234, lo=-8.0, hi=8.0):
     """points uniform in [-8,8]^3 (seed 1234) and unit directions (seed 1235)."""
