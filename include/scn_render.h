@@ -10,8 +10,10 @@
  *     bsdfs/LambertBsdf.cpp): cosine-weighted direction about the sampled gradient, weight = albedo;
  *   - a constant infinite-sphere emitter (primitives/InfiniteSphere.cpp), gathered when a path leaves the cube;
  *   - Russian roulette as PathTracer.cpp:146-152, integrator max_bounces.
- * Next-event estimation (TraceBase.cpp:346-420) is NOT done: with a uniform environment the estimator without it has the same
- * expectation, so images agree with the reference's in the mean, not sample by sample (the reference's per-tile sampler streams
+ * With scene.nee == 0 next-event estimation (TraceBase.cpp:346-420) is NOT done: with a uniform environment the estimator
+ * without it has the same expectation.  With scene.nee == 1 the stage runs the reference's estimator (light + phase sampling with
+ * MIS at every medium scatter, mirror / conductor phase functions over the 1D-noise NEE entry points, one quad emitter), in RGB.
+ * Either way images agree with the reference's in the mean, not sample by sample (the reference's per-tile sampler streams
  * cannot be reproduced on a wavefront; this stage draws from a counter-based hash of (pixel, sample, bounce, dimension)).
  *
  * Tiles are the reference's 16 x 16 tiles in diceTiles order (row-major, integrators/path_tracer/PathTraceIntegrator.cpp:26-41);
@@ -37,7 +39,24 @@ typedef struct scn_wf_scene {
     float albedo;                                /* lambert "albedo" of the brdf phase     */
     int32_t max_bounces;                         /* integrator "max_bounces"               */
     uint32_t scene_seed;                         /* TraceableScene seed (-s)               */
+    /* ---- next-event estimation stage; everything below is ignored while nee == 0 ---- */
+    int32_t nee;                                 /* 1: the reference's estimator — volumeEstimateDirect at every medium scatter
+                                                    (TraceBase.cpp:346-420, 506-518, 539-563), emitters seen directly only by
+                                                    unscattered paths (TraceBase.cpp:629-637); RGB                                 */
+    int32_t phase_type;                          /* SCN_WF_PHASE_*: bsdf of the "brdf" phase function                             */
+    float albedo_rgb[3];                         /* bsdf "albedo"                                                                 */
+    float eta[3], k[3];                          /* conductor: complex IOR (bsdfs/ComplexIorData.hpp), 0/0 = perfect mirror       */
+    float env_rgb[3];                            /* infinite_sphere "emission"                                                    */
+    int32_t env_sample;                          /* infinite_sphere "sample"                                                      */
+    int32_t has_quad;                            /* one quad emitter (primitives/Quad.cpp), null bsdf                             */
+    int32_t quad_first;                          /* 1 when the quad precedes the infinite_sphere in "primitives" (light order)    */
+    float quad_base[3], quad_edge0[3], quad_edge1[3]; /* Quad::prepareForRender (:296-316)                                        */
+    float quad_rgb[3];                           /* quad "emission"                                                               */
 } scn_wf_scene;
+
+#define SCN_WF_PHASE_LAMBERT 0
+#define SCN_WF_PHASE_MIRROR 1
+#define SCN_WF_PHASE_CONDUCTOR 2
 
 /* Per-path buffers of one wavefront (all device pointers, n elements each, caller-owned). */
 typedef struct scn_wf_paths {
@@ -47,7 +66,23 @@ typedef struct scn_wf_paths {
     float *throughput;      /* path throughput (grey)                                                  */
     float *radiance;        /* radiance carried by the path once it has ended                          */
     uint8_t *alive;         /* 1 while the path still needs medium queries                             */
+    /* nee stage only (NULL otherwise): green / blue planes (throughput / radiance above are the red ones) and the
+     * "has scattered in the medium" flag (wasSpecular == false, PathTracer.cpp:58, TraceBase.cpp:544) */
+    float *throughput_gb[2];
+    float *radiance_gb[2];
+    uint8_t *scattered;
 } scn_wf_paths;
+
+/* Shadow rays of one half of volumeSampleDirect (TraceBase.cpp:444-456): the light-sampled ray (volumeLightSample) or the
+ * phase-sampled ray (volumePhaseSample).  scn_wf_nee_setup fills rays / state (a copy of the path's MediumState with the segment
+ * index advanced, lastAniso replaced by neeGrad for specular phase functions: TraceBase.cpp:372-376, 543-546) and the unshadowed
+ * contribution; the caller runs scn_transmittance_batch(rays, state) -> T; scn_wf_nee_gather adds contrib * T to the radiance. */
+typedef struct scn_wf_shadow {
+    scn_rays rays;
+    scn_state state;
+    float *T;
+    float *contrib[3];
+} scn_wf_shadow;
 
 /* Number of tiles of an image (diceTiles). */
 uint32_t scn_wf_tile_count(uint32_t res_x, uint32_t res_y);
@@ -67,6 +102,15 @@ int scn_wf_shade(const scn_wf_scene *scene, const scn_medium *m, const scn_wf_pa
 /* framebuffer[local_pixel] += sum over the spp_count samples of the pixel (fixed order: deterministic).  Replaces
  * OutputBuffer::addSample (PathTraceIntegrator.cpp:159). */
 int scn_wf_accumulate(const float *radiance, float *framebuffer, size_t n_pixels, uint32_t spp_count, void *stream);
+
+/* volumeEstimateDirect for every path that scattered at `bounce` (TraceBase.cpp:346-420, 444-518): light choice
+ * (chooseLight over approximateRadiance), Quad / InfiniteSphere sampleDirect and directPdf, phase eval / sample / pdf of the
+ * Lambert, mirror and conductor bsdfs — for the specular ones through neePDF / neeGrad of the medium's 1D noise
+ * (bsdfs/ConductorBsdf.cpp:58-140, bsdfs/MirrorBsdf.cpp:40-110) — and the power heuristic.  Call between
+ * scn_sample_distance_batch and scn_wf_shade. */
+int scn_wf_nee_setup(const scn_wf_scene *scene, const scn_medium *m, const scn_wf_paths *paths, const scn_wf_shadow *light_rays,
+                     const scn_wf_shadow *phase_rays, size_t n, int32_t bounce, void *stream);
+int scn_wf_nee_gather(const scn_wf_paths *paths, const scn_wf_shadow *light_rays, const scn_wf_shadow *phase_rays, size_t n, void *stream);
 
 #ifdef __cplusplus
 }

@@ -215,6 +215,8 @@ extern "C" {
 
 const char *scn_last_error(void) { return last_error(); }
 int scn_abi_version(void) { return SCN_ABI_VERSION; }
+// internal (not in include/scn.h): the wavefront stage's NEE kernels (scn_render.cu) call the medium's device functions directly
+extern "C" const void *scn_internal_params(const scn_medium *m) { return m ? &m->P : nullptr; }
 int scn_desc_default(scn_medium_desc *d) { return desc_default(d); }
 int scn_desc_from_json(const char *json, scn_medium_desc *d) { return desc_from_json(json, d); }
 

@@ -41,13 +41,72 @@ __device__ __forceinline__ bool wf_cube(const scn_wf_scene &S, float ox, float o
 struct WfPaths {
     float *ox, *oy, *oz, *dx, *dy, *dz, *tmin, *tmax, *u; uint32_t *px, *py, *spp, *seg;
     uint8_t *first_scatter; float *last_val, *lgx, *lgy, *lgz; int32_t *bounce, *last_gp_id; float *info_t; uint8_t *scheme; float *ctx[7];
-    const uint8_t *ok, *exited; const float *t, *gx, *gy, *gz, *weight;
+    const uint8_t *ok, *exited, *sample_scheme; const float *t, *gx, *gy, *gz, *weight;
     float *throughput, *radiance; uint8_t *alive;
+    float *thr_gb[2], *rad_gb[2]; uint8_t *scattered; // nee stage: green / blue planes, "has scattered" flag
 };
 
 __device__ __forceinline__ void wf_finish(const WfPaths &W, size_t i, float radiance) {
     W.radiance[i] = radiance; W.alive[i] = 0; W.bounce[i] = WF_DEAD_BOUNCE;
 }
+// nee stage: radiance accumulates along the path (emission += throughput * ..., PathTracer.cpp:72, TraceBase.cpp:546)
+__device__ __forceinline__ void wf_finish_rgb(const WfPaths &W, size_t i, f3 add) {
+    W.radiance[i] += add.x; W.rad_gb[0][i] += add.y; W.rad_gb[1][i] += add.z; W.alive[i] = 0; W.bounce[i] = WF_DEAD_BOUNCE;
+}
+
+// ---- emitters of the nee stage ------------------------------------------------------------------------------------------------
+struct WfQuad { f3 base, e0, e1, n; float area, inv_uv0, inv_uv1; };
+// Quad::prepareForRender (primitives/Quad.cpp:296-316)
+__device__ __forceinline__ WfQuad wf_quad(const scn_wf_scene &S) {
+    WfQuad q; q.base = F3(S.quad_base[0], S.quad_base[1], S.quad_base[2]); q.e0 = F3(S.quad_edge0[0], S.quad_edge0[1], S.quad_edge0[2]); q.e1 = F3(S.quad_edge1[0], S.quad_edge1[1], S.quad_edge1[2]);
+    f3 n = F3(q.e1.y * q.e0.z - q.e1.z * q.e0.y, q.e1.z * q.e0.x - q.e1.x * q.e0.z, q.e1.x * q.e0.y - q.e1.y * q.e0.x);
+    q.area = sqrtf(n.x * n.x + n.y * n.y + n.z * n.z); q.n = F3(n.x / q.area, n.y / q.area, n.z / q.area);
+    q.inv_uv0 = 1.0f / (q.e0.x * q.e0.x + q.e0.y * q.e0.y + q.e0.z * q.e0.z); q.inv_uv1 = 1.0f / (q.e1.x * q.e1.x + q.e1.y * q.e1.y + q.e1.z * q.e1.z);
+    return q;
+}
+__device__ __forceinline__ float dot3(f3 a, f3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
+__device__ __forceinline__ f3 sub3(f3 a, f3 b) { return F3(a.x - b.x, a.y - b.y, a.z - b.z); }
+__device__ __forceinline__ f3 cross3(f3 a, f3 b) { return F3(a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x); }
+__device__ __forceinline__ f3 norm3(f3 a) { const float il = 1.0f / sqrtf(dot3(a, a)); return F3(a.x * il, a.y * il, a.z * il); }
+// Quad::intersect (primitives/Quad.cpp:71-97) over [0, inf): distance and side
+__device__ __forceinline__ bool wf_quad_hit(const WfQuad &q, f3 o, f3 d, float &t, bool &back) {
+    const float ndw = dot3(d, q.n);
+    if (fabsf(ndw) < 1e-6f) return false;
+    t = dot3(q.n, sub3(q.base, o)) / ndw;
+    if (t < 0.f) return false;
+    const f3 v = sub3(F3(o.x + t * d.x, o.y + t * d.y, o.z + t * d.z), q.base);
+    const float l0 = dot3(v, q.e0) * q.inv_uv0, l1 = dot3(v, q.e1) * q.inv_uv1;
+    if (l0 < 0.f || l0 > 1.f || l1 < 0.f || l1 > 1.f) return false;
+    back = ndw >= 0.f;
+    return true;
+}
+// Quad::approximateRadiance (primitives/Quad.cpp:256-279): solid angle of the spherical quadrilateral x emission
+__device__ __forceinline__ float wf_quad_approx(const WfQuad &q, f3 p, float emax) {
+    const f3 R0 = sub3(q.base, p);
+    if (dot3(R0, q.n) >= 0.f) return 0.f;
+    const f3 R1 = F3(R0.x + q.e0.x, R0.y + q.e0.y, R0.z + q.e0.z), R2 = F3(R1.x + q.e1.x, R1.y + q.e1.y, R1.z + q.e1.z), R3 = F3(R0.x + q.e1.x, R0.y + q.e1.y, R0.z + q.e1.z);
+    const f3 n0 = norm3(cross3(R0, R1)), n1 = norm3(cross3(R1, R2)), n2 = norm3(cross3(R2, R3)), n3 = norm3(cross3(R3, R0));
+    const float Q = acosf(dot3(n0, n1)) + acosf(dot3(n1, n2)) + acosf(dot3(n2, n3)) + acosf(dot3(n3, n0));
+    return (6.283185307179586f - fabsf(Q)) * emax;
+}
+// Fresnel::conductorReflectance (bsdfs/Fresnel.hpp:102-123)
+__device__ __forceinline__ float wf_conductor(float eta, float k, float c) {
+    if (eta == 0.f && k == 0.f) return 1.f;
+    const float c2 = c * c, s2 = fmaxf(1.0f - c2, 0.0f), s4 = s2 * s2;
+    const float inner = eta * eta - k * k - s2;
+    const float ab = sqrtf(fmaxf(inner * inner + 4.0f * eta * eta * k * k, 0.0f));
+    const float a = sqrtf(fmaxf((ab + inner) * 0.5f, 0.0f));
+    const float Rs = ((ab + c2) - (2.0f * a * c)) / ((ab + c2) + (2.0f * a * c));
+    const float Rp = ((c2 * ab + s4) - (2.0f * a * c * s2)) / ((c2 * ab + s4) + (2.0f * a * c * s2));
+    return 0.5f * (Rs + Rs * Rp);
+}
+// albedo x Fresnel of the specular phase bsdfs (bsdfs/MirrorBsdf.cpp:38, bsdfs/ConductorBsdf.cpp:66)
+__device__ __forceinline__ f3 wf_specular_weight(const scn_wf_scene &S, float cos_i) {
+    f3 w = F3(S.albedo_rgb[0], S.albedo_rgb[1], S.albedo_rgb[2]);
+    if (S.phase_type == SCN_WF_PHASE_CONDUCTOR) { w.x *= wf_conductor(S.eta[0], S.k[0], cos_i); w.y *= wf_conductor(S.eta[1], S.k[1], cos_i); w.z *= wf_conductor(S.eta[2], S.k[2], cos_i); }
+    return w;
+}
+__device__ __forceinline__ float power_heuristic(float a, float b) { return (a * a) / (a * a + b * b); }
 
 // PathTracer::traceSample :31-59 — camera sample, first intersection with the scene (the cube), medium state reset
 __global__ void __launch_bounds__(WF_BLOCK) k_wf_raygen(const scn_wf_scene S, const WfPaths W, uint32_t tile_first, uint32_t spp_first, uint32_t spp_count, size_t n) {
@@ -64,6 +123,7 @@ __global__ void __launch_bounds__(WF_BLOCK) k_wf_raygen(const scn_wf_scene S, co
     if (W.scheme) W.scheme[i] = SCN_SCHEME_UNI;
     if (W.ctx[0]) for (int j = 0; j < 7; ++j) W.ctx[j][i] = 0.f;
     W.throughput[i] = 1.f; W.radiance[i] = 0.f; W.alive[i] = 1;
+    if (S.nee) { W.thr_gb[0][i] = 1.f; W.thr_gb[1][i] = 1.f; W.rad_gb[0][i] = 0.f; W.rad_gb[1][i] = 0.f; W.scattered[i] = 0; }
     W.ox[i] = S.cam_pos[0]; W.oy[i] = S.cam_pos[1]; W.oz[i] = S.cam_pos[2]; W.dx[i] = 0.f; W.dy[i] = 0.f; W.dz[i] = 1.f; W.tmin[i] = 0.f; W.tmax[i] = 0.f; W.u[i] = 0.f;
     if (x >= S.res_x || y >= S.res_y) { wf_finish(W, i, 0.f); return; } // padding of an edge tile
     // Mat4f::lookAt (math/Mat4f.cpp:175-187) and PinholeCamera::sampleDirection (cameras/PinholeCamera.cpp:70-86), box filter
@@ -80,7 +140,13 @@ __global__ void __launch_bounds__(WF_BLOCK) k_wf_raygen(const scn_wf_scene S, co
     const f3 d = F3(r.x * ld.x + uu.x * ld.y + f.x * ld.z, r.y * ld.x + uu.y * ld.y + f.y * ld.z, r.z * ld.x + uu.z * ld.y + f.z * ld.z);
     W.dx[i] = d.x; W.dy[i] = d.y; W.dz[i] = d.z;
     float t0, t1;
-    if (!wf_cube(S, S.cam_pos[0], S.cam_pos[1], S.cam_pos[2], d.x, d.y, d.z, t0, t1)) { wf_finish(W, i, S.emission); return; } // straight to the environment
+    const bool hit_cube = wf_cube(S, S.cam_pos[0], S.cam_pos[1], S.cam_pos[2], d.x, d.y, d.z, t0, t1);
+    if (S.nee) { // an unscattered path sees the emitters directly (wasSpecular starts true, PathTracer.cpp:58)
+        float tq; bool back;
+        const bool hit_quad = S.has_quad && wf_quad_hit(wf_quad(S), F3(S.cam_pos[0], S.cam_pos[1], S.cam_pos[2]), d, tq, back);
+        if (hit_quad && (!hit_cube || tq < t0)) { wf_finish_rgb(W, i, back ? F3(0, 0, 0) : F3(S.quad_rgb[0], S.quad_rgb[1], S.quad_rgb[2])); return; }
+        if (!hit_cube) { wf_finish_rgb(W, i, F3(S.env_rgb[0], S.env_rgb[1], S.env_rgb[2])); return; }
+    } else if (!hit_cube) { wf_finish(W, i, S.emission); return; } // straight to the environment
     W.tmin[i] = t0; W.tmax[i] = t1; W.u[i] = wf_rand(x, y, spp, 0u, 0u, S.scene_seed);
 }
 
@@ -121,6 +187,207 @@ __global__ void __launch_bounds__(WF_BLOCK) k_wf_shade(const scn_wf_scene S, con
     W.throughput[i] = thr;
 }
 
+// ---- nee stage ----------------------------------------------------------------------------------------------------------------
+struct WfShadow {
+    float *ox, *oy, *oz, *dx, *dy, *dz, *tmin, *tmax, *u; uint32_t *px, *py, *spp, *seg;
+    uint8_t *first_scatter; float *last_val, *lgx, *lgy, *lgz; int32_t *bounce, *last_gp_id; float *info_t;
+    float *T; float *contrib[3];
+};
+__device__ __forceinline__ void wf_shadow_clear(const WfShadow &H, const WfPaths &W, size_t i) {
+    // a ray of zero length: the march returns T = 1 without a single evaluation; contrib = 0 makes it irrelevant
+    H.ox[i] = 0.f; H.oy[i] = 0.f; H.oz[i] = 0.f; H.dx[i] = 0.f; H.dy[i] = 0.f; H.dz[i] = 1.f; H.tmin[i] = 0.f; H.tmax[i] = 0.f; H.u[i] = 0.f;
+    H.px[i] = W.px[i]; H.py[i] = W.py[i]; H.spp[i] = W.spp[i]; H.seg[i] = 0u;
+    H.first_scatter[i] = 1; H.last_val[i] = 0.f; H.lgx[i] = 0.f; H.lgy[i] = 0.f; H.lgz[i] = 0.f; H.bounce[i] = 0; H.last_gp_id[i] = 0; H.info_t[i] = 0.f;
+    H.contrib[0][i] = 0.f; H.contrib[1][i] = 0.f; H.contrib[2][i] = 0.f;
+}
+// the shadow ray p + t d, t in [0, far], through the medium inside the cube; MediumState copy with the segment index advanced
+// (TraceBase.cpp:543-546) and lastAniso = `aniso` (the sampled gradient, or neeGrad for a specular light sample: :372-376)
+__device__ __forceinline__ void wf_shadow_write(const scn_wf_scene &S, const WfShadow &H, const WfPaths &W, size_t i, f3 p, f3 d, float far_t, f3 aniso, float u, f3 contrib) {
+    float t0, t1;
+    const bool inside = wf_cube(S, p.x, p.y, p.z, d.x, d.y, d.z, t0, t1);
+    H.ox[i] = p.x; H.oy[i] = p.y; H.oz[i] = p.z; H.dx[i] = d.x; H.dy[i] = d.y; H.dz[i] = d.z; H.tmin[i] = 0.f; H.tmax[i] = inside ? fminf(t1, far_t) : 0.f; H.u[i] = u;
+    H.seg[i] = W.seg[i] + 1u;
+    H.first_scatter[i] = W.first_scatter[i]; H.last_val[i] = W.last_val[i]; H.lgx[i] = aniso.x; H.lgy[i] = aniso.y; H.lgz[i] = aniso.z;
+    H.bounce[i] = W.bounce[i]; H.last_gp_id[i] = W.last_gp_id[i]; H.info_t[i] = W.info_t[i];
+    H.contrib[0][i] = contrib.x; H.contrib[1][i] = contrib.y; H.contrib[2][i] = contrib.z;
+}
+
+// volumeEstimateDirect (TraceBase.cpp:506-518) for the paths that scattered at `bounce`: chooseLight (:457-504), volumeLightSample
+// (:346-388) into L, volumePhaseSample (:390-420) into Q.  The transmittance along both rays is computed by the caller.
+__global__ void __launch_bounds__(WF_BLOCK) k_wf_nee_setup(const __grid_constant__ Params P, const scn_wf_scene S, const WfPaths W, const WfShadow L, const WfShadow Q, int32_t bounce, size_t n) {
+    const size_t i = (size_t)blockIdx.x * WF_BLOCK + threadIdx.x;
+    if (i >= n) return;
+    wf_shadow_clear(L, W, i); wf_shadow_clear(Q, W, i);
+    if (!W.alive[i] || !W.ok[i] || W.exited[i]) return;
+    if (!(bounce < S.max_bounces - 1)) return; // TraceBase.cpp:546
+    const uint32_t x = W.px[i], y = W.py[i], spp = W.spp[i], nb = (uint32_t)bounce | 0x8000u;
+    const float wq = W.weight[i];
+    const f3 thr = F3(W.throughput[i] * wq, W.thr_gb[0][i] * wq, W.thr_gb[1][i] * wq);
+    const float t = W.t[i];
+    const f3 dir = F3(W.dx[i], W.dy[i], W.dz[i]);
+    const f3 p = F3(W.ox[i] + t * dir.x, W.oy[i] + t * dir.y, W.oz[i] + t * dir.z);
+    const f3 g = F3(W.gx[i], W.gy[i], W.gz[i]);
+    // BRDFPhaseFunction::setEventIsectInfo (phasefunctions/BRDFPhaseFunction.cpp:27-44)
+    const Frame fr = make_frame(norm3(g));
+    const f3 nrm = fr.n;
+    const f3 wi = norm3(to_local(fr, F3(-dir.x, -dir.y, -dir.z)));
+    const int sch = (int)W.sample_scheme[i];
+    const bool specular = S.phase_type != SCN_WF_PHASE_LAMBERT;
+    const Info info = {x, y, spp, W.seg[i], S.scene_seed, W.info_t[i]};
+    Coeff c; c.vs = 0.f; c.gs = F3(0, 0, 0); c.org = F3(0, 0, 0);
+    if (W.ctx[0]) { c.vs = W.ctx[0][i]; c.gs = F3(W.ctx[1][i], W.ctx[2][i], W.ctx[3][i]); c.org = F3(W.ctx[4][i], W.ctx[5][i], W.ctx[6][i]); }
+    // ---- chooseLight: lights in primitive order, pdf ~ approximateRadiance
+    const WfQuad quad = wf_quad(S);
+    const float env_max = fmaxf(S.env_rgb[0], fmaxf(S.env_rgb[1], S.env_rgb[2])), quad_max = fmaxf(S.quad_rgb[0], fmaxf(S.quad_rgb[1], S.quad_rgb[2]));
+    const bool env_light = S.env_sample && env_max > 0.f, quad_light = S.has_quad && quad_max > 0.f;
+    bool use_quad; float lw;
+    if (env_light && quad_light) {
+        const float pe = 6.283185307179586f * env_max, pq = wf_quad_approx(quad, p, quad_max), total = pe + pq;
+        if (total == 0.f) return;
+        const float tsel = wf_rand(x, y, spp, nb, 0u, S.scene_seed) * total;
+        const float first = S.quad_first ? pq : pe;
+        use_quad = (tsel < first) ? (S.quad_first != 0) : (S.quad_first == 0);
+        lw = total / (use_quad ? pq : pe);
+    } else if (env_light || quad_light) { use_quad = quad_light; lw = 1.f; }
+    else return;
+    const f3 Le = use_quad ? F3(S.quad_rgb[0], S.quad_rgb[1], S.quad_rgb[2]) : F3(S.env_rgb[0], S.env_rgb[1], S.env_rgb[2]);
+    const f3 aniso = F3(W.lgx[i], W.lgy[i], W.lgz[i]); // state.lastAniso after the query = the sampled gradient
+
+    // ---- volumeLightSample
+    if (!(specular && sch == SCN_SCHEME_UNI)) {
+        const float u1 = wf_rand(x, y, spp, nb, 1u, S.scene_seed), u2 = wf_rand(x, y, spp, nb, 2u, S.scene_seed);
+        bool okl = true; f3 d = F3(0, 0, 1); float dist = INFINITY, pdf_l = 0.f;
+        if (use_quad) { // Quad::sampleDirect (primitives/Quad.cpp:172-187)
+            if (dot3(quad.n, sub3(p, quad.base)) <= 0.f) okl = false;
+            else {
+                const f3 qp = F3(quad.base.x + u1 * quad.e0.x + u2 * quad.e1.x, quad.base.y + u1 * quad.e0.y + u2 * quad.e1.y, quad.base.z + u1 * quad.e0.z + u2 * quad.e1.z);
+                d = sub3(qp, p); const float r2 = dot3(d, d); dist = sqrtf(r2); d = F3(d.x / dist, d.y / dist, d.z / dist);
+                pdf_l = r2 / (-dot3(quad.n, d) * quad.area);
+            }
+        } else { // InfiniteSphere::sampleDirect, constant emission (primitives/InfiniteSphere.cpp:161-167)
+            const float phi = u1 * 6.283185307179586f, z = u2 * 2.0f - 1.0f, r = sqrtf(fmaxf(1.0f - z * z, 0.0f));
+            d = F3(cosf(phi) * r, sinf(phi) * r, z); pdf_l = 0.07957747154594767f;
+        }
+        if (okl) {
+            const f3 wo = norm3(to_local(fr, d));
+            f3 f = F3(0, 0, 0); float phase_pdf = 0.f; f3 an = aniso;
+            if (!specular) { // LambertBsdf::eval / pdf (bsdfs/LambertBsdf.cpp:40-47, 62-69)
+                if (wi.z > 0.f && wo.z > 0.f) { const float k = 0.3183098861837907f * wo.z; f = F3(S.albedo_rgb[0] * k, S.albedo_rgb[1] * k, S.albedo_rgb[2] * k); phase_pdf = fabsf(wo.z) * 0.3183098861837907f; }
+            } else { // MirrorBsdf / ConductorBsdf::eval, pdf, evalGrad with a sampling scheme other than UNI
+                const f3 nl = F3((wi.x + wo.x) * 0.5f, (wi.y + wo.y) * 0.5f, (wi.z + wo.z) * 0.5f);
+                const f3 nw = norm3(to_global(fr, nl));
+                const float pn = nee_pdf(P, c, dir, nw, p, t, info);
+                const f3 w = wf_specular_weight(S, wi.z);
+                f = F3(w.x * pn, w.y * pn, w.z * pn); phase_pdf = pn;
+                Nee o; nee_shared(P, c, dir, nw, p, info, o); an = F3(o.dist * nw.x, o.dist * nw.y, o.dist * nw.z);
+            }
+            if (!(f.x == 0.f && f.y == 0.f && f.z == 0.f)) {
+                // attenuatedEmission (TraceBase.cpp:156-185): the light must be hit at the expected distance; evalDirect
+                bool vis = true; float far_t = INFINITY; f3 e = Le;
+                float tq; bool back;
+                const bool hq = S.has_quad && wf_quad_hit(quad, p, d, tq, back);
+                if (use_quad) { if (!hq || tq * (1.0f + 1e-3f) < dist) vis = false; else { far_t = tq; if (back) e = F3(0, 0, 0); } }
+                else if (hq) vis = false; // the quad (null bsdf: no forward lobe) blocks the way to the environment (TraceBase.cpp:92-94)
+                if (vis && !(e.x == 0.f && e.y == 0.f && e.z == 0.f)) {
+                    float mis = 1.f;
+                    if (!(specular && sch == SCN_SCHEME_NEE)) mis = power_heuristic(pdf_l, phase_pdf);
+                    const float k = lw * mis / pdf_l;
+                    wf_shadow_write(S, L, W, i, p, d, far_t, an, wf_rand(x, y, spp, nb, 3u, S.scene_seed), F3(thr.x * f.x * e.x * k, thr.y * f.y * e.y * k, thr.z * f.z * e.z * k));
+                }
+            }
+        }
+    }
+    // ---- volumePhaseSample
+    if (!(specular && sch == SCN_SCHEME_NEE)) {
+        f3 wo, w; float pdf_p; bool oks = true;
+        if (!specular) { // LambertBsdf::sample (bsdfs/LambertBsdf.cpp:26-38)
+            if (wi.z <= 0.f) oks = false;
+            const float u1 = wf_rand(x, y, spp, nb, 5u, S.scene_seed), u2 = wf_rand(x, y, spp, nb, 6u, S.scene_seed);
+            const float phi = 6.283185307179586f * u1, r = sqrtf(u2);
+            wo = F3(cosf(phi) * r, sinf(phi) * r, sqrtf(fmaxf(1.0f - u2, 0.0f)));
+            w = F3(S.albedo_rgb[0], S.albedo_rgb[1], S.albedo_rgb[2]); pdf_p = fabsf(wo.z) * 0.3183098861837907f;
+        } else { // MirrorBsdf / ConductorBsdf::sample
+            wo = F3(-wi.x, -wi.y, wi.z); w = wf_specular_weight(S, wi.z); pdf_p = 1.f;
+            if (sch != SCN_SCHEME_UNI) pdf_p = nee_pdf(P, c, dir, nrm, p, t, info);
+        }
+        if (oks) {
+            const f3 d = norm3(to_global(fr, wo));
+            bool vis = true; float far_t = INFINITY, dpdf = 0.07957747154594767f; f3 e = Le;
+            float tq; bool back;
+            const bool hq = S.has_quad && wf_quad_hit(quad, p, d, tq, back);
+            if (use_quad) {
+                if (!hq) vis = false;
+                else { far_t = tq; if (back) e = F3(0, 0, 0); const float ndw = dot3(quad.n, d), tt = dot3(quad.n, sub3(quad.base, p)) / ndw; dpdf = tt * tt / (fabsf(ndw) * quad.area); } // Quad::directPdf (:216-223)
+            } else if (hq) vis = false;
+            if (vis && !(e.x == 0.f && e.y == 0.f && e.z == 0.f)) {
+                float mis = 1.f;
+                if (!specular || sch != SCN_SCHEME_UNI) mis = power_heuristic(pdf_p, dpdf);
+                const float k = lw * mis;
+                wf_shadow_write(S, Q, W, i, p, d, far_t, aniso, wf_rand(x, y, spp, nb, 4u, S.scene_seed), F3(thr.x * w.x * e.x * k, thr.y * w.y * e.y * k, thr.z * w.z * e.z * k));
+            }
+        }
+    }
+}
+
+__global__ void __launch_bounds__(WF_BLOCK) k_wf_nee_gather(const WfPaths W, const WfShadow L, const WfShadow Q, size_t n) {
+    const size_t i = (size_t)blockIdx.x * WF_BLOCK + threadIdx.x;
+    if (i >= n) return;
+    const float tl = L.T[i], tq = Q.T[i];
+    W.radiance[i] += L.contrib[0][i] * tl + Q.contrib[0][i] * tq;
+    W.rad_gb[0][i] += L.contrib[1][i] * tl + Q.contrib[1][i] * tq;
+    W.rad_gb[1][i] += L.contrib[2][i] * tl + Q.contrib[2][i] * tq;
+}
+
+// k_wf_shade with the reference's bookkeeping of direct emitter hits: an emitter met by the path itself counts only while the path
+// has not scattered (TraceBase.cpp:592-596, 629-637 with wasSpecular = false after handleVolume); RGB throughput.
+__global__ void __launch_bounds__(WF_BLOCK) k_wf_shade_nee(const scn_wf_scene S, const WfPaths W, int32_t bounce, size_t n) {
+    const size_t i = (size_t)blockIdx.x * WF_BLOCK + threadIdx.x;
+    if (i >= n || !W.alive[i]) return;
+    if (!W.ok[i]) { wf_finish_rgb(W, i, F3(0, 0, 0)); return; }
+    const float wq = W.weight[i];
+    f3 thr = F3(W.throughput[i] * wq, W.thr_gb[0][i] * wq, W.thr_gb[1][i] * wq);
+    const float t = W.t[i];
+    const f3 dir = F3(W.dx[i], W.dy[i], W.dz[i]);
+    const f3 p = F3(W.ox[i] + t * dir.x, W.oy[i] + t * dir.y, W.oz[i] + t * dir.z);
+    if (W.exited[i]) {
+        f3 e = F3(0, 0, 0);
+        if (!W.scattered[i]) {
+            float tq; bool back;
+            if (S.has_quad && wf_quad_hit(wf_quad(S), p, dir, tq, back)) e = back ? F3(0, 0, 0) : F3(S.quad_rgb[0], S.quad_rgb[1], S.quad_rgb[2]);
+            else e = F3(S.env_rgb[0], S.env_rgb[1], S.env_rgb[2]);
+        }
+        wf_finish_rgb(W, i, F3(thr.x * e.x, thr.y * e.y, thr.z * e.z)); return;
+    }
+    W.scattered[i] = 1;
+    const uint32_t x = W.px[i], y = W.py[i], spp = W.spp[i];
+    const Frame fr = make_frame(norm3(F3(W.gx[i], W.gy[i], W.gz[i])));
+    const f3 wi = norm3(to_local(fr, F3(-dir.x, -dir.y, -dir.z)));
+    f3 wo, w;
+    if (S.phase_type == SCN_WF_PHASE_LAMBERT) {
+        if (wi.z <= 0.f) { wf_finish_rgb(W, i, F3(0, 0, 0)); return; } // "Wrong normal direction in sampling phase function" (TraceBase.cpp:551-554)
+        const float u1 = wf_rand(x, y, spp, (uint32_t)bounce, 1u, S.scene_seed), u2 = wf_rand(x, y, spp, (uint32_t)bounce, 2u, S.scene_seed);
+        const float phi = 6.283185307179586f * u1, r = sqrtf(u2);
+        wo = F3(cosf(phi) * r, sinf(phi) * r, sqrtf(fmaxf(1.0f - u2, 0.0f)));
+        w = F3(S.albedo_rgb[0], S.albedo_rgb[1], S.albedo_rgb[2]);
+    } else { wo = F3(-wi.x, -wi.y, wi.z); w = wf_specular_weight(S, wi.z); }
+    thr = F3(thr.x * w.x, thr.y * w.y, thr.z * w.z);
+    const float tmax = fmaxf(thr.x, fmaxf(thr.y, thr.z));
+    if (tmax == 0.f) { wf_finish_rgb(W, i, F3(0, 0, 0)); return; }
+    const float rp = fmaxf(fabsf(thr.x), fmaxf(fabsf(thr.y), fabsf(thr.z)));
+    if (bounce > 2 && rp < 0.1f) {
+        if (wf_rand(x, y, spp, (uint32_t)bounce, 3u, S.scene_seed) < rp) thr = F3(thr.x / rp, thr.y / rp, thr.z / rp);
+        else { wf_finish_rgb(W, i, F3(0, 0, 0)); return; }
+    }
+    if (bounce + 1 >= S.max_bounces) { wf_finish_rgb(W, i, F3(0, 0, 0)); return; }
+    const f3 d = norm3(to_global(fr, wo));
+    float t0, t1;
+    if (!wf_cube(S, p.x, p.y, p.z, d.x, d.y, d.z, t0, t1)) { wf_finish_rgb(W, i, F3(0, 0, 0)); return; }
+    W.ox[i] = p.x; W.oy[i] = p.y; W.oz[i] = p.z; W.dx[i] = d.x; W.dy[i] = d.y; W.dz[i] = d.z; W.tmin[i] = 0.f; W.tmax[i] = t1;
+    W.u[i] = wf_rand(x, y, spp, (uint32_t)bounce + 1u, 0u, S.scene_seed);
+    W.seg[i] = (uint32_t)bounce + 1u;
+    W.throughput[i] = thr.x; W.thr_gb[0][i] = thr.y; W.thr_gb[1][i] = thr.z;
+}
+
 __global__ void __launch_bounds__(WF_BLOCK) k_wf_accumulate(const float *__restrict__ radiance, float *__restrict__ fb, size_t n_pixels, uint32_t spp_count) {
     const size_t i = (size_t)blockIdx.x * WF_BLOCK + threadIdx.x;
     if (i >= n_pixels) return;
@@ -144,8 +411,29 @@ static int wf_paths(const scn_wf_paths *p, WfPaths &W, bool need_samples) {
     W.last_gp_id = s.last_gp_id; W.info_t = s.info_t; W.scheme = s.scheme;
     bool all = true; for (int j = 0; j < 7; ++j) all = all && s.ctx[j];
     for (int j = 0; j < 7; ++j) W.ctx[j] = all ? s.ctx[j] : nullptr;
-    W.ok = o.ok; W.exited = o.exited; W.t = o.t; W.gx = o.gx; W.gy = o.gy; W.gz = o.gz; W.weight = o.weight;
+    W.ok = o.ok; W.exited = o.exited; W.sample_scheme = o.scheme; W.t = o.t; W.gx = o.gx; W.gy = o.gy; W.gz = o.gz; W.weight = o.weight;
     W.throughput = p->throughput; W.radiance = p->radiance; W.alive = p->alive;
+    W.thr_gb[0] = p->throughput_gb[0]; W.thr_gb[1] = p->throughput_gb[1]; W.rad_gb[0] = p->radiance_gb[0]; W.rad_gb[1] = p->radiance_gb[1]; W.scattered = p->scattered;
+    return SCN_OK;
+}
+static int wf_nee_arrays(const scn_wf_paths *p) {
+    if (!p->throughput_gb[0] || !p->throughput_gb[1] || !p->radiance_gb[0] || !p->radiance_gb[1] || !p->scattered)
+        return set_error(SCN_EINVAL, "wavefront: scene.nee needs throughput_gb, radiance_gb and scattered");
+    return SCN_OK;
+}
+static int wf_shadow(const scn_wf_shadow *h, WfShadow &H) {
+    const scn_rays &r = h->rays; const scn_state &s = h->state;
+    if (!r.ox || !r.oy || !r.oz || !r.dx || !r.dy || !r.dz || !r.tmin || !r.tmax || !r.u || !r.px || !r.py || !r.spp || !r.segment)
+        return set_error(SCN_EINVAL, "shadow rays: every ray array is required");
+    if (!s.first_scatter || !s.last_val || !s.last_gx || !s.last_gy || !s.last_gz || !s.bounce || !s.last_gp_id || !s.info_t)
+        return set_error(SCN_EINVAL, "shadow rays: state arrays are required");
+    if (!h->T || !h->contrib[0] || !h->contrib[1] || !h->contrib[2]) return set_error(SCN_EINVAL, "shadow rays: T and contrib are required");
+    H.ox = (float *)r.ox; H.oy = (float *)r.oy; H.oz = (float *)r.oz; H.dx = (float *)r.dx; H.dy = (float *)r.dy; H.dz = (float *)r.dz;
+    H.tmin = (float *)r.tmin; H.tmax = (float *)r.tmax; H.u = (float *)r.u;
+    H.px = (uint32_t *)r.px; H.py = (uint32_t *)r.py; H.spp = (uint32_t *)r.spp; H.seg = (uint32_t *)r.segment;
+    H.first_scatter = s.first_scatter; H.last_val = s.last_val; H.lgx = s.last_gx; H.lgy = s.last_gy; H.lgz = s.last_gz; H.bounce = s.bounce;
+    H.last_gp_id = s.last_gp_id; H.info_t = s.info_t;
+    H.T = h->T; H.contrib[0] = h->contrib[0]; H.contrib[1] = h->contrib[1]; H.contrib[2] = h->contrib[2];
     return SCN_OK;
 }
 static int wf_check(const char *what) { cudaError_t e = cudaGetLastError(); if (e != cudaSuccess) return set_error(SCN_ECUDA, "%s: %s", what, cudaGetErrorString(e)); return SCN_OK; }
@@ -153,6 +441,7 @@ static int wf_check(const char *what) { cudaError_t e = cudaGetLastError(); if (
 } // namespace scn
 
 using namespace scn;
+extern "C" const void *scn_internal_params(const scn_medium *m); // scn_api.cu: the medium's kernel parameters (scn::Params)
 extern "C" {
 
 uint32_t scn_wf_tile_count(uint32_t res_x, uint32_t res_y) { return ((res_x + SCN_WF_TILE - 1) / SCN_WF_TILE) * ((res_y + SCN_WF_TILE - 1) / SCN_WF_TILE); }
@@ -165,6 +454,7 @@ int scn_wf_raygen(const scn_wf_scene *scene, const scn_medium *m, uint32_t tile_
     if (tile_first + tile_count > scn_wf_tile_count(scene->res_x, scene->res_y)) return set_error(SCN_EINVAL, "raygen: tile range outside the image");
     if (n == 0) return SCN_OK;
     WfPaths W; if (int rc = wf_paths(paths, W, false)) return rc;
+    if (scene->nee) if (int rc = wf_nee_arrays(paths)) return rc;
     k_wf_raygen<<<(unsigned)((n + WF_BLOCK - 1) / WF_BLOCK), WF_BLOCK, 0, (cudaStream_t)stream>>>(*scene, W, tile_first, spp_first, spp_count, n);
     return wf_check("k_wf_raygen");
 }
@@ -175,8 +465,39 @@ int scn_wf_shade(const scn_wf_scene *scene, const scn_medium *m, const scn_wf_pa
     if (!scene || !paths) return set_error(SCN_EINVAL, "null argument");
     if (n == 0) return SCN_OK;
     WfPaths W; if (int rc = wf_paths(paths, W, true)) return rc;
+    if (scene->nee) {
+        if (int rc = wf_nee_arrays(paths)) return rc;
+        k_wf_shade_nee<<<(unsigned)((n + WF_BLOCK - 1) / WF_BLOCK), WF_BLOCK, 0, (cudaStream_t)stream>>>(*scene, W, bounce, n);
+        return wf_check("k_wf_shade_nee");
+    }
     k_wf_shade<<<(unsigned)((n + WF_BLOCK - 1) / WF_BLOCK), WF_BLOCK, 0, (cudaStream_t)stream>>>(*scene, W, bounce, n);
     return wf_check("k_wf_shade");
+}
+
+int scn_wf_nee_setup(const scn_wf_scene *scene, const scn_medium *m, const scn_wf_paths *paths, const scn_wf_shadow *light_rays, const scn_wf_shadow *phase_rays,
+                     size_t n, int32_t bounce, void *stream) {
+    if (!scene || !m || !paths || !light_rays || !phase_rays) return set_error(SCN_EINVAL, "null argument");
+    if (!scene->nee) return set_error(SCN_EINVAL, "scn_wf_nee_setup: scene.nee is 0");
+    if (n == 0) return SCN_OK;
+    const Params *P = (const Params *)scn_internal_params(m);
+    if (scene->phase_type != SCN_WF_PHASE_LAMBERT && !P->sampling_1d)
+        return set_error(SCN_EUNSUPPORTED, "mirror / conductor phase functions need a 1D-sampling medium (neePDF / neeGrad are 1D-noise entry points)");
+    WfPaths W; if (int rc = wf_paths(paths, W, true)) return rc;
+    if (int rc = wf_nee_arrays(paths)) return rc;
+    if (!paths->samples.scheme) return set_error(SCN_EINVAL, "scn_wf_nee_setup: samples.scheme is required");
+    WfShadow L, Q; if (int rc = wf_shadow(light_rays, L)) return rc; if (int rc = wf_shadow(phase_rays, Q)) return rc;
+    k_wf_nee_setup<<<(unsigned)((n + WF_BLOCK - 1) / WF_BLOCK), WF_BLOCK, 0, (cudaStream_t)stream>>>(*P, *scene, W, L, Q, bounce, n);
+    return wf_check("k_wf_nee_setup");
+}
+
+int scn_wf_nee_gather(const scn_wf_paths *paths, const scn_wf_shadow *light_rays, const scn_wf_shadow *phase_rays, size_t n, void *stream) {
+    if (!paths || !light_rays || !phase_rays) return set_error(SCN_EINVAL, "null argument");
+    if (n == 0) return SCN_OK;
+    WfPaths W; if (int rc = wf_paths(paths, W, false)) return rc;
+    if (int rc = wf_nee_arrays(paths)) return rc;
+    WfShadow L, Q; if (int rc = wf_shadow(light_rays, L)) return rc; if (int rc = wf_shadow(phase_rays, Q)) return rc;
+    k_wf_nee_gather<<<(unsigned)((n + WF_BLOCK - 1) / WF_BLOCK), WF_BLOCK, 0, (cudaStream_t)stream>>>(W, L, Q, n);
+    return wf_check("k_wf_nee_gather");
 }
 
 int scn_wf_accumulate(const float *radiance, float *framebuffer, size_t n_pixels, uint32_t spp_count, void *stream) {

@@ -21,11 +21,24 @@ TILE = 16
 class WfScene(C.Structure):
     _fields_ = [("cam_pos", C.c_float * 3), ("cam_look_at", C.c_float * 3), ("cam_up", C.c_float * 3), ("fov_deg", C.c_float),
                 ("res_x", C.c_uint32), ("res_y", C.c_uint32), ("cube_center", C.c_float * 3), ("cube_half", C.c_float * 3),
-                ("emission", C.c_float), ("albedo", C.c_float), ("max_bounces", C.c_int32), ("scene_seed", C.c_uint32)]
+                ("emission", C.c_float), ("albedo", C.c_float), ("max_bounces", C.c_int32), ("scene_seed", C.c_uint32),
+                ("nee", C.c_int32), ("phase_type", C.c_int32), ("albedo_rgb", C.c_float * 3), ("eta", C.c_float * 3), ("k", C.c_float * 3),
+                ("env_rgb", C.c_float * 3), ("env_sample", C.c_int32), ("has_quad", C.c_int32), ("quad_first", C.c_int32),
+                ("quad_base", C.c_float * 3), ("quad_edge0", C.c_float * 3), ("quad_edge1", C.c_float * 3), ("quad_rgb", C.c_float * 3)]
 
 
 class WfPaths(C.Structure):
-    _fields_ = [("rays", abi.Rays), ("state", abi.State), ("samples", abi.Samples), ("throughput", abi.f32p), ("radiance", abi.f32p), ("alive", abi.u8p)]
+    _fields_ = [("rays", abi.Rays), ("state", abi.State), ("samples", abi.Samples), ("throughput", abi.f32p), ("radiance", abi.f32p), ("alive", abi.u8p),
+                ("throughput_gb", abi.f32p * 2), ("radiance_gb", abi.f32p * 2), ("scattered", abi.u8p)]
+
+
+class WfShadow(C.Structure):
+    _fields_ = [("rays", abi.Rays), ("state", abi.State), ("T", abi.f32p), ("contrib", abi.f32p * 3)]
+
+
+PHASE_LAMBERT, PHASE_MIRROR, PHASE_CONDUCTOR = 0, 1, 2
+# bsdfs/ComplexIorData.hpp (the materials the BASELINE configs name)
+COMPLEX_IOR = {"Cu": ((0.2004376970, 0.9240334304, 1.1022119527), (3.9129485033, 2.4528477015, 2.1421879552))}
 
 
 RENDER_SYMBOLS = {
@@ -33,6 +46,8 @@ RENDER_SYMBOLS = {
     "scn_wf_raygen": (C.c_int, [C.POINTER(WfScene), abi.MediumP, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.POINTER(WfPaths), C.c_size_t, C.c_void_p]),
     "scn_wf_shade": (C.c_int, [C.POINTER(WfScene), abi.MediumP, C.POINTER(WfPaths), C.c_size_t, C.c_int32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p]),
     "scn_wf_accumulate": (C.c_int, [abi.f32p, abi.f32p, C.c_size_t, C.c_uint32, C.c_void_p]),
+    "scn_wf_nee_setup": (C.c_int, [C.POINTER(WfScene), abi.MediumP, C.POINTER(WfPaths), C.POINTER(WfShadow), C.POINTER(WfShadow), C.c_size_t, C.c_int32, C.c_void_p]),
+    "scn_wf_nee_gather": (C.c_int, [C.POINTER(WfPaths), C.POINTER(WfShadow), C.POINTER(WfShadow), C.c_size_t, C.c_void_p]),
 }
 
 
@@ -68,7 +83,56 @@ def scene_from_json(scene):
     s.albedo = float(alb if np.isscalar(alb) else np.mean(alb))
     s.max_bounces = int(scene.get("integrator", {}).get("max_bounces", 64))
     s.scene_seed = int(scene.get("renderer", {}).get("seed", 0xBA5EBA11)) & 0xFFFFFFFF
+    # ---- nee stage: phase bsdf, RGB emitters, one quad light (include/scn_render.h)
+    rgb = lambda v, d=1.0: [float(v)] * 3 if np.isscalar(v) else [float(x) for x in v]
+    bsdf = med.get("phase_function", {}).get("bsdf", {})
+    kind = bsdf.get("type", "lambert")
+    s.albedo_rgb[:] = rgb(bsdf.get("albedo", 1.0 if kind != "lambert" else 0.5))
+    if kind == "lambert":
+        s.phase_type = PHASE_LAMBERT
+        s.albedo_rgb[:] = rgb(alb)
+    elif kind == "mirror":
+        s.phase_type = PHASE_MIRROR
+    elif kind == "conductor":
+        s.phase_type = PHASE_CONDUCTOR
+        if "eta" in bsdf and "k" in bsdf:
+            s.eta[:] = rgb(bsdf["eta"]); s.k[:] = rgb(bsdf["k"])
+        else:
+            name = bsdf.get("material", "Cu")
+            if name not in COMPLEX_IOR:
+                raise ValueError("conductor material %r is not in this stage's table" % name)
+            s.eta[:], s.k[:] = COMPLEX_IOR[name]
+    else:
+        raise ValueError("phase bsdf %r is not covered by the wavefront stage (lambert, mirror, conductor)" % kind)
+    s.env_rgb[:] = rgb(em) if env else [0.0] * 3
+    s.env_sample = int(bool(env.get("sample", True))) if env else 0
+    prims = scene["primitives"]
+    quad = next((p for p in prims if p["type"] == "quad" and "emission" in p), None)
+    s.has_quad = int(quad is not None)
+    if quad is not None:
+        base, e0, e1 = quad_geometry(quad.get("transform", {}))
+        s.quad_base[:], s.quad_edge0[:], s.quad_edge1[:] = base, e0, e1
+        s.quad_rgb[:] = rgb(quad["emission"])
+        s.quad_first = int(env is None or prims.index(quad) < prims.index(env))
+    specular = s.phase_type != PHASE_LAMBERT
+    s.nee = int(bool(scene.get("integrator", {}).get("scn_nee", specular or quad is not None)))
     return s
+
+
+def quad_geometry(tr):
+    """Quad::prepareForRender (primitives/Quad.cpp:296-304) over the JSON transform (io/JsonUtils.cpp: scale, then rotation
+    "rotation" in degrees through Mat4f::rotYXZ, then position; io/JsonPtr.cpp:108-183): base corner and the two edges."""
+    pos = np.array(tr.get("position", [0, 0, 0]), np.float64)
+    sc = tr.get("scale", [1, 1, 1]); sc = np.array([sc] * 3 if np.isscalar(sc) else sc, np.float64)
+    r = np.radians(np.array(tr.get("rotation", [0, 0, 0]), np.float64))
+    c, sn = np.cos(r), np.sin(r)
+    R = np.array([[c[1] * c[2] - sn[1] * sn[0] * sn[2], -c[1] * sn[2] - sn[1] * sn[0] * c[2], -sn[1] * c[0]],
+                  [c[0] * sn[2], c[0] * c[2], -sn[0]],
+                  [sn[1] * c[2] + c[1] * sn[0] * sn[2], -sn[1] * sn[2] + c[1] * sn[0] * c[2], c[1] * c[0]]])  # Mat4f::rotYXZ (math/Mat4f.cpp:118-130)
+    M = R @ np.diag(sc)  # io/JsonPtr.cpp:161-174: axes scaled, then rotated
+    e0, e1 = M @ np.array([1.0, 0, 0]), M @ np.array([0, 0, 1.0])
+    base = pos - 0.5 * e0 - 0.5 * e1
+    return [float(v) for v in base], [float(v) for v in e0], [float(v) for v in e1]
 
 
 def tile_range(n_tiles, rank, world):
@@ -81,16 +145,20 @@ def tile_range(n_tiles, rank, world):
 class WavefrontRenderer:
     """One GPU's share of a render: tiles [tile_first, tile_first + tile_count)."""
 
-    def __init__(self, scene_json, device=0, rank=0, world=1, max_paths=1 << 22):
+    def __init__(self, scene_json, device=0, rank=0, world=1, max_paths=1 << 22, nee=None):
         self.lib = load()
         self.scene = scene_from_json(scene_json)
+        if nee is not None:
+            self.scene.nee = int(bool(nee))
+        self.nee = bool(self.scene.nee)
         self.dev = torch.device("cuda", device)
         self.medium = SparseConvolutionNoiseMedium.from_json(scene_json["media"][0], device)
         self.n_tiles = int(self.lib.scn_wf_tile_count(self.scene.res_x, self.scene.res_y))
         self.tile_first, self.tile_count = tile_range(self.n_tiles, rank, world)
         self.n_pixels = self.tile_count * TILE * TILE
         self.max_paths = max_paths
-        self.framebuffer = torch.zeros(max(self.n_pixels, 1), dtype=torch.float32, device=self.dev)
+        self.framebuffer = torch.zeros(max(self.n_pixels, 1), dtype=torch.float32, device=self.dev)  # red (or grey) plane
+        self.framebuffer_gb = [torch.zeros(max(self.n_pixels, 1), dtype=torch.float32, device=self.dev) for _ in range(2)] if self.nee else None
         self.spp_done = 0
         self.queries = 0
         self._buf_n = 0
@@ -123,6 +191,28 @@ class WavefrontRenderer:
         for k, dt in SAMPLE_FIELDS:
             setattr(p.samples, k, ptr(self.samples[k], ct[dt]))
         p.throughput, p.radiance, p.alive = ptr(self.throughput, abi.f32p), ptr(self.radiance, abi.f32p), ptr(self.alive, abi.u8p)
+        if self.nee:
+            self.thr_gb, self.rad_gb, self.scattered = [mk(np.float32), mk(np.float32)], [mk(np.float32), mk(np.float32)], mk(np.uint8)
+            for j in range(2):
+                p.throughput_gb[j] = ptr(self.thr_gb[j], abi.f32p); p.radiance_gb[j] = ptr(self.rad_gb[j], abi.f32p)
+            p.scattered = ptr(self.scattered, abi.u8p)
+            self.shadow = []
+            for _ in range(2):  # light-sampled and phase-sampled shadow rays (volumeLightSample / volumePhaseSample)
+                h = WfShadow()
+                rays = {k: mk(np.float32) for k in RAY_F}; rays.update({k: mk(np.uint32) for k in RAY_U})
+                state = {k: mk(dt) for k, dt in STATE_FIELDS}
+                for k in RAY_F:
+                    setattr(h.rays, k, ptr(rays[k], abi.f32p))
+                for k in RAY_U:
+                    setattr(h.rays, k, ptr(rays[k], abi.u32p))
+                h.rays.scene_seed = self.scene.scene_seed
+                for k, dt in STATE_FIELDS:
+                    setattr(h.state, k, ptr(state[k], ct[dt]))
+                T, contrib = mk(np.float32), [mk(np.float32) for _ in range(3)]
+                h.T = ptr(T, abi.f32p)
+                for j in range(3):
+                    h.contrib[j] = ptr(contrib[j], abi.f32p)
+                self.shadow.append({"c": h, "rays": rays, "state": state, "T": T, "contrib": contrib})
         self.paths = p
         self._buf_n = n
 
@@ -144,15 +234,26 @@ class WavefrontRenderer:
                 if count_queries:
                     self.queries += int(self.alive.sum().item())
                 self.medium.sample_distance(self.rays, self.state, scene_seed=self.scene.scene_seed, out=self.samples, stream=stream)
+                if self.nee and bounce < self.scene.max_bounces - 1:  # volumeEstimateDirect at every scatter of this bounce
+                    L, Q = self.shadow
+                    abi.check(self.lib.scn_wf_nee_setup(C.byref(self.scene), self.medium._h, C.byref(self.paths), C.byref(L["c"]), C.byref(Q["c"]), n, bounce, sp))
+                    for h in (L, Q):
+                        self.medium.transmittance(h["rays"], h["state"], scene_seed=self.scene.scene_seed, out=h["T"], stream=stream)
+                    abi.check(self.lib.scn_wf_nee_gather(C.byref(self.paths), C.byref(L["c"]), C.byref(Q["c"]), n, sp))
                 abi.check(self.lib.scn_wf_shade(C.byref(self.scene), self.medium._h, C.byref(self.paths), n, bounce, self.spp_done + done, c, self.tile_first, sp))
             abi.check(self.lib.scn_wf_accumulate(C.cast(C.c_void_p(self.radiance.data_ptr()), abi.f32p), C.cast(C.c_void_p(self.framebuffer.data_ptr()), abi.f32p),
                                                  self.n_pixels, c, sp))
+            if self.nee:
+                for j in range(2):
+                    abi.check(self.lib.scn_wf_accumulate(C.cast(C.c_void_p(self.rad_gb[j].data_ptr()), abi.f32p), C.cast(C.c_void_p(self.framebuffer_gb[j].data_ptr()), abi.f32p),
+                                                         self.n_pixels, c, sp))
             done += c
         self.spp_done += spp
 
-    def local_image(self):
-        """This rank's tiles as [tile_count, 16, 16] mean radiance."""
-        return (self.framebuffer[: self.n_pixels] / max(self.spp_done, 1)).view(self.tile_count, TILE, TILE)
+    def local_image(self, channel=0):
+        """This rank's tiles as [tile_count, 16, 16] mean radiance (channel 0 = red or grey; 1, 2 = green, blue of an nee render)."""
+        fb = self.framebuffer if channel == 0 or not self.nee else self.framebuffer_gb[channel - 1]
+        return (fb[: self.n_pixels] / max(self.spp_done, 1)).view(self.tile_count, TILE, TILE)
 
     def close(self):
         self.medium.close()
@@ -165,10 +266,18 @@ def assemble_image(tiles, res_x, res_y):
     return img[:res_y, :res_x].contiguous()
 
 
-def gather_image(renderer, world=1):
+def gather_image_rgb(renderer, world=1):
+    """[res_y, res_x, 3]: three gather_image calls for an nee (RGB) render, the grey image repeated otherwise."""
+    if not getattr(renderer, "nee", False):
+        g = gather_image(renderer, world)
+        return torch.stack([g, g, g], -1)
+    return torch.stack([gather_image(renderer, world, ch) for ch in range(3)], -1)
+
+
+def gather_image(renderer, world=1, channel=0):
     """The one collective of a render: all ranks' framebuffer slices -> the full image on every rank (NCCL all_gather over
     NVLink; 4 B per pixel).  Slices are padded to the largest tile count so that the gather is a single call."""
-    local = renderer.local_image()
+    local = renderer.local_image(channel) if channel else renderer.local_image()
     if world > 1:
         import torch.distributed as dist
         cap = (renderer.n_tiles + world - 1) // world

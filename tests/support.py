@@ -112,12 +112,23 @@ MEDIA = {
 IS_1D = {k: bool(v.get("1D_sampling")) for k, v in MEDIA.items()}
 
 
-def appendix_a_scene(medium_json, res, spp, max_bounces=8):
-    """SURVEY.md Appendix A.1 around `medium_json`: cube [-1.5,1.5]^3 holding the medium, constant environment, pinhole camera.
-    Box reconstruction filter (the wavefront stage's), no embree ("scene_bvh": false), no output files."""
+QUAD_LIGHT = {"type": "quad", "transform": {"position": [0, 4, 0], "scale": [2, 2, 2], "rotation": [180, 0, 0]}, "emission": 20.0, "bsdf": {"type": "null"}}
+
+
+def c4_scene_medium():
+    """the C4 medium (1D, Renewal+, correlationXY, mis) with a copper conductor as the phase bsdf."""
+    m = copy.deepcopy(MEDIA["c4_1d_renewalplus_xy_mis"])
+    m["phase_function"] = {"type": "brdf", "bsdf": {"type": "conductor", "material": "Cu"}}
+    return m
+
+
+def appendix_a_scene(medium_json, res, spp, max_bounces=8, quad=False, env=1.0):
+    """SURVEY.md Appendix A.1 around `medium_json`: cube [-1.5,1.5]^3 holding the medium, constant environment, pinhole camera
+    (A.3 with quad=True: plus the quad area light).  Box reconstruction filter (the wavefront stage's), no embree
+    ("scene_bvh": false), no output files."""
     return {"media": [medium_json], "bsdfs": [],
             "primitives": [{"type": "cube", "transform": {"scale": [3, 3, 3]}, "bsdf": {"type": "forward"}, "int_medium": medium_json["name"]},
-                           {"type": "infinite_sphere", "emission": 1.0, "sample": True}],
+                           {"type": "infinite_sphere", "emission": env, "sample": True}] + ([copy.deepcopy(QUAD_LIGHT)] if quad else []),
             "camera": {"type": "pinhole", "resolution": [res, res], "fov": 35, "tonemap": "gamma", "reconstruction_filter": "box",
                        "transform": {"position": [0, 0, 5], "look_at": [0, 0, 0], "up": [0, 1, 0]}},
             "integrator": {"type": "path_tracer", "min_bounces": 0, "max_bounces": max_bounces},

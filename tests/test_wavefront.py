@@ -129,34 +129,53 @@ def rel_mse(a, b):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("name", ["c1", "c3", "c5"])
-def test_images_vs_reference_renderer(name):
+@pytest.mark.parametrize("name,nee", [("c1", False), ("c3", False), ("c5", False), ("c1", True), ("c3", True), ("c5", True),
+                                      ("c3_quad", True), ("c4", True), ("c4_nee", True)])
+def test_images_vs_reference_renderer(name, nee):
     """Image-level parity with the UNMODIFIED reference renderer (tests/golden/render_*.npz, made by make_ref_images.py from
-    oracle/_ref): the reference does next-event estimation, the wavefront stage does not (same expectation under the constant
-    environment), and the two use different path samplers, so agreement is statistical.  Stated bounds, with A, B the two
-    reference renders (different sampler seeds) and R their mean:
+    oracle/_ref).  nee=False: the stage without next-event estimation (same expectation under the constant environment);
+    nee=True: the reference's estimator (light + phase sampling with MIS at every scatter; c4 / c4_nee: copper conductor phase
+    bsdf through neePDF / neeGrad, quad light).  The two renderers use different path samplers, so agreement is statistical.
+    Stated bounds, with A, B the two reference renders (different sampler seeds) and R their mean:
       * equal spp:  relMSE(GPU, R) <= 2 x relMSE(A, B)                 
       * 16 x spp:   relMSE(GPU, R) <= 0.75 x relMSE(A, B)              (a bias would not average out)
-      * |mean(GPU) - mean(R)| <= 1 % of mean(R) at 16 x spp."""
+      * |mean(GPU) - mean(R)| <= 1 % of mean(R) at 16 x spp (2 % for the specular scenes, whose reference is noisier)."""
     import json
     import torch
     from sparse_conv_gpis_tungsten_b200 import render as R
     g = np.load(os.path.join(S.GOLDEN_DIR, "render_%s.npz" % name), allow_pickle=False)
     scene = json.loads(str(g["scene_json"]))
     A, B = g["images"][0], g["images"][1]
+    rgb = A.ndim == 3
     ref = 0.5 * (A.astype(np.float64) + B)
     floor = rel_mse(A, B)
     spp = int(scene["renderer"]["spp"])
-    r = R.WavefrontRenderer(scene, device=0)
+    r = R.WavefrontRenderer(scene, device=0, nee=nee)
+    assert r.nee == nee
+    grab = (lambda: R.gather_image_rgb(r, 1).cpu().numpy()) if rgb else (lambda: R.gather_image(r, 1).cpu().numpy())
     r.render(spp)
-    img = R.gather_image(r, 1).cpu().numpy()
+    img = grab()
     assert img.shape == ref.shape
     e1 = rel_mse(img, ref)
     r.render(15 * spp)
-    img16 = R.gather_image(r, 1).cpu().numpy()
+    img16 = grab()
     e16 = rel_mse(img16, ref)
     r.close()
-    print("%s: relMSE(A,B)=%.3e  GPU@%dspp=%.3e  GPU@%dspp=%.3e  means ref %.4f gpu %.4f" % (name, floor, spp, e1, 16 * spp, e16, ref.mean(), img16.mean()))
+    print("%s nee=%d: relMSE(A,B)=%.3e  GPU@%dspp=%.3e  GPU@%dspp=%.3e  means ref %.4f gpu %.4f" % (name, nee, floor, spp, e1, 16 * spp, e16, ref.mean(), img16.mean()))
     assert e1 <= 2.0 * floor, (e1, floor)
     assert e16 <= 0.75 * floor, (e16, floor)
-    assert abs(img16.mean() - ref.mean()) <= 0.01 * ref.mean()
+    assert abs(img16.mean() - ref.mean()) <= (0.02 if name.startswith("c4") else 0.01) * ref.mean()
+
+
+def test_quad_geometry_matches_reference_transform():
+    """Quad::prepareForRender over the JSON transform of SURVEY.md Appendix A.3: a 2 x 2 quad at y = 4 facing down."""
+    from sparse_conv_gpis_tungsten_b200 import render as R
+    base, e0, e1 = R.quad_geometry(S.QUAD_LIGHT["transform"])
+    assert np.allclose(e0, [2, 0, 0], atol=1e-6) and np.allclose(e1, [0, 0, -2], atol=1e-6) and np.allclose(base, [-1, 4, 1], atol=1e-6)
+    n = np.cross(e1, e0)
+    assert np.allclose(n / np.linalg.norm(n), [0, -1, 0], atol=1e-6)
+    sc = R.scene_from_json(S.appendix_a_scene(S.c4_scene_medium(), 32, 1, quad=True))
+    assert sc.nee == 1 and sc.phase_type == R.PHASE_CONDUCTOR and sc.has_quad == 1 and sc.quad_first == 0
+    assert abs(sc.eta[0] - 0.2004377) < 1e-6 and abs(sc.k[2] - 2.142188) < 1e-5 and list(sc.quad_rgb) == [20.0, 20.0, 20.0]
+    sc = R.scene_from_json(S.appendix_a_scene(S.MEDIA["c1_sphere_3d_none"], 32, 1))
+    assert sc.nee == 0 and sc.phase_type == R.PHASE_LAMBERT and abs(sc.albedo_rgb[1] - 0.8) < 1e-6
