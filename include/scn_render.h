@@ -111,6 +111,9 @@ int scn_wf_accumulate(const float *radiance, float *framebuffer, size_t n_pixels
 int scn_wf_nee_setup(const scn_wf_scene *scene, const scn_medium *m, const scn_wf_paths *paths, const scn_wf_shadow *light_rays,
                      const scn_wf_shadow *phase_rays, size_t n, int32_t bounce, void *stream);
 int scn_wf_nee_gather(const scn_wf_paths *paths, const scn_wf_shadow *light_rays, const scn_wf_shadow *phase_rays, size_t n, void *stream);
+/* The sample clamp of PathTraceIntegrator::renderTile (PathTraceIntegrator.cpp:148-156) on the finished paths of an nee (RGB)
+ * wavefront: a sample with a NaN, an infinite component or a component above 65536 becomes black.  Call before scn_wf_accumulate. */
+int scn_wf_clamp_samples(const scn_wf_paths *paths, size_t n, void *stream);
 
 #ifdef __cplusplus
 }

@@ -388,6 +388,16 @@ __global__ void __launch_bounds__(WF_BLOCK) k_wf_shade_nee(const scn_wf_scene S,
     W.throughput[i] = thr.x; W.thr_gb[0][i] = thr.y; W.thr_gb[1][i] = thr.z;
 }
 
+// PathTraceIntegrator::renderTile (integrators/path_tracer/PathTraceIntegrator.cpp:148-156): a sample with an infinite component, a
+// component above 65536 or a NaN is replaced by black before it reaches the framebuffer
+__global__ void __launch_bounds__(WF_BLOCK) k_wf_clamp_rgb(float *__restrict__ r, float *__restrict__ g, float *__restrict__ b, size_t n) {
+    const size_t i = (size_t)blockIdx.x * WF_BLOCK + threadIdx.x;
+    if (i >= n) return;
+    const float x = r[i], y = g[i], z = b[i];
+    const bool bad = isinf(x) || isinf(y) || isinf(z) || x > 65536.f || y > 65536.f || z > 65536.f || isnan(x) || isnan(y) || isnan(z);
+    if (bad) { r[i] = 0.f; g[i] = 0.f; b[i] = 0.f; }
+}
+
 __global__ void __launch_bounds__(WF_BLOCK) k_wf_accumulate(const float *__restrict__ radiance, float *__restrict__ fb, size_t n_pixels, uint32_t spp_count) {
     const size_t i = (size_t)blockIdx.x * WF_BLOCK + threadIdx.x;
     if (i >= n_pixels) return;
@@ -488,6 +498,15 @@ int scn_wf_nee_setup(const scn_wf_scene *scene, const scn_medium *m, const scn_w
     WfShadow L, Q; if (int rc = wf_shadow(light_rays, L)) return rc; if (int rc = wf_shadow(phase_rays, Q)) return rc;
     k_wf_nee_setup<<<(unsigned)((n + WF_BLOCK - 1) / WF_BLOCK), WF_BLOCK, 0, (cudaStream_t)stream>>>(*P, *scene, W, L, Q, bounce, n);
     return wf_check("k_wf_nee_setup");
+}
+
+int scn_wf_clamp_samples(const scn_wf_paths *paths, size_t n, void *stream) {
+    if (!paths) return set_error(SCN_EINVAL, "null argument");
+    if (n == 0) return SCN_OK;
+    if (!paths->radiance) return set_error(SCN_EINVAL, "wavefront: radiance is required");
+    if (int rc = wf_nee_arrays(paths)) return rc;
+    k_wf_clamp_rgb<<<(unsigned)((n + WF_BLOCK - 1) / WF_BLOCK), WF_BLOCK, 0, (cudaStream_t)stream>>>(paths->radiance, paths->radiance_gb[0], paths->radiance_gb[1], n);
+    return wf_check("k_wf_clamp_rgb");
 }
 
 int scn_wf_nee_gather(const scn_wf_paths *paths, const scn_wf_shadow *light_rays, const scn_wf_shadow *phase_rays, size_t n, void *stream) {

@@ -48,6 +48,7 @@ RENDER_SYMBOLS = {
     "scn_wf_accumulate": (C.c_int, [abi.f32p, abi.f32p, C.c_size_t, C.c_uint32, C.c_void_p]),
     "scn_wf_nee_setup": (C.c_int, [C.POINTER(WfScene), abi.MediumP, C.POINTER(WfPaths), C.POINTER(WfShadow), C.POINTER(WfShadow), C.c_size_t, C.c_int32, C.c_void_p]),
     "scn_wf_nee_gather": (C.c_int, [C.POINTER(WfPaths), C.POINTER(WfShadow), C.POINTER(WfShadow), C.c_size_t, C.c_void_p]),
+    "scn_wf_clamp_samples": (C.c_int, [C.POINTER(WfPaths), C.c_size_t, C.c_void_p]),
 }
 
 
@@ -241,6 +242,8 @@ class WavefrontRenderer:
                         self.medium.transmittance(h["rays"], h["state"], scene_seed=self.scene.scene_seed, out=h["T"], stream=stream)
                     abi.check(self.lib.scn_wf_nee_gather(C.byref(self.paths), C.byref(L["c"]), C.byref(Q["c"]), n, sp))
                 abi.check(self.lib.scn_wf_shade(C.byref(self.scene), self.medium._h, C.byref(self.paths), n, bounce, self.spp_done + done, c, self.tile_first, sp))
+            if self.nee:
+                abi.check(self.lib.scn_wf_clamp_samples(C.byref(self.paths), n, sp))
             abi.check(self.lib.scn_wf_accumulate(C.cast(C.c_void_p(self.radiance.data_ptr()), abi.f32p), C.cast(C.c_void_p(self.framebuffer.data_ptr()), abi.f32p),
                                                  self.n_pixels, c, sp))
             if self.nee:
