@@ -228,29 +228,31 @@ def run_gpu(args):
     e2e_value = world * ne * e2e_steps / float(te.item())
     same = all(torch.equal(a, b[:ne].cpu()) for a, b in zip(ho, outs))
 
-    # ---- tile-sharded wavefront render: every rank renders its contiguous tile range, one NCCL all_gather of the slices
-    render = None
+    # ---- tile-sharded wavefront renders: every rank renders its contiguous tile range, one NCCL all_gather of the slices.
+    #      C1 = Appendix A.1 without next-event estimation; C4 = Appendix A.3 (copper conductor phase bsdf, quad light, NEE + MIS)
+    render, render_c4 = None, None
     if not args.no_extras:
         from sparse_conv_gpis_tungsten_b200 import render as R
-        res, spp = 512, 16
-        sc = {"media": [S.MEDIA["c1_sphere_3d_none"]],
-              "primitives": [{"type": "cube", "transform": {"scale": [3, 3, 3]}, "bsdf": {"type": "forward"}, "int_medium": "gpis"},
-                             {"type": "infinite_sphere", "emission": 1.0, "sample": True}],
-              "camera": {"type": "pinhole", "resolution": [res, res], "fov": 35, "transform": {"position": [0, 0, 5], "look_at": [0, 0, 0], "up": [0, 1, 0]}},
-              "integrator": {"type": "path_tracer", "max_bounces": 8}, "renderer": {"spp": spp, "adaptive_sampling": False}}
-        wr = R.WavefrontRenderer(sc, device=local, rank=rank, world=world); wr.render(1); wr.close()  # warm-up
-        wr = R.WavefrontRenderer(sc, device=local, rank=rank, world=world)
-        torch.cuda.synchronize()
-        if world > 1:
-            dist.barrier()
-        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        a.record(stream); wr.render(spp); img = R.gather_image(wr, world); b.record(stream); torch.cuda.synchronize()
-        tr = torch.tensor([a.elapsed_time(b)], device=dev, dtype=torch.float64)
-        if world > 1:
-            dist.all_reduce(tr, op=dist.ReduceOp.MAX)
-        render = {"workload": "C1 scene (Appendix A.1) %dx%d @%dspp, max_bounces 8, 16x16 tiles sharded over %d GPU(s), one all_gather" % (res, res, spp, world),
-                  "ms": float(tr.item()), "camera_paths_per_s": res * res * spp / (float(tr.item()) * 1e-3), "mean_radiance": float(img.mean().item())}
-        wr.close()
+
+        def timed_render(sc, spp, label):
+            wr = R.WavefrontRenderer(sc, device=local, rank=rank, world=world); wr.render(1); wr.close()  # warm-up
+            wr = R.WavefrontRenderer(sc, device=local, rank=rank, world=world)
+            torch.cuda.synchronize()
+            if world > 1:
+                dist.barrier()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record(stream); wr.render(spp); img = R.gather_image_rgb(wr, world); b.record(stream); torch.cuda.synchronize()
+            tr = torch.tensor([a.elapsed_time(b)], device=dev, dtype=torch.float64)
+            if world > 1:
+                dist.all_reduce(tr, op=dist.ReduceOp.MAX)
+            res = sc["camera"]["resolution"]
+            out = {"workload": "%s %dx%d @%dspp, max_bounces %d, nee %s, 16x16 tiles sharded over %d GPU(s), one all_gather" % (label, res[0], res[1], spp, sc["integrator"]["max_bounces"], "on" if wr.nee else "off", world),
+                   "ms": float(tr.item()), "camera_paths_per_s": res[0] * res[1] * spp / (float(tr.item()) * 1e-3), "mean_radiance": float(img.mean().item())}
+            wr.close()
+            return out
+
+        render = timed_render(S.appendix_a_scene(S.MEDIA["c1_sphere_3d_none"], 512, 16), 16, "C1 scene (Appendix A.1)")
+        render_c4 = timed_render(S.appendix_a_scene(S.c4_scene_medium(), 512, 16, quad=True), 16, "C4 scene (Appendix A.3: 1D Renewal+ XY, copper conductor, quad light, mis)")
 
     if rank != 0:
         if world > 1:
@@ -289,6 +291,7 @@ def run_gpu(args):
     extra = {"e2e_matches_device": bool(same)}
     if render is not None:
         extra["render"] = render
+        extra["render_c4"] = render_c4
     if not args.no_extras:
         sweep = {}
         for iso in (True, False):
@@ -302,34 +305,31 @@ def run_gpu(args):
                 sweep["%s_N%d" % ("iso" if iso else "world", dens)] = {"evals_per_s": ev, "issue_frac": ev * w_issue(dens) / issue_peak}
                 m2.close()
         extra["sweep"] = sweep
-        # medium queries: camera rays through the Appendix-A.1 cube (C1 medium), 2^20 rays
+        # medium queries (sampleDistance): 2^20 camera rays through the Appendix-A cube, one medium per BASELINE render config
         nq = 1 << 20
         rays, st = S.camera_rays(nq, seed=11)
-        g = S.GpuImpl(S.MEDIA["c1_sphere_3d_none"], device=local)
-        r, s = g._rays_state(rays, st)
-        out = g.m.sample_distance(r, s, scene_seed=1, count_evals=True)
-        torch.cuda.synchronize()
-        r, s = g._rays_state(rays, st)
-        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        a.record(stream); out = g.m.sample_distance(r, s, scene_seed=1, out=out, stream=stream); b.record(stream); torch.cuda.synchronize()
-        qs = a.elapsed_time(b) * 1e-3
-        ev = int(out["n_evals"].view(torch.int32).to(torch.int64).sum().item())
-        extra["medium_queries"] = {"workload": "C1 medium (sphere mean, SE, 3D iso, none/single), 2^20 camera rays, step 0.01",
-                                   "queries_per_s": nq / qs, "noise_evals_per_s": ev / qs, "evals_per_query": ev / nq}
-        g.close()
+        for key, name, what in (("medium_queries", "c1_sphere_3d_none", "C1 medium (sphere mean, SE, 3D iso, none/single)"),
+                                ("medium_queries_c3", "c3_1d_renewal", "C3 medium (1D sampling, renewal)"),
+                                ("medium_queries_c4", "c4_1d_renewalplus_xy_mis", "C4 medium (1D sampling, renewal+, correlationXY, mis)"),
+                                ("medium_queries_c5", "c5_multires_nonstat_renewalplus", "C5 medium (multi-resolution non-stationary, renewal+)")):
+            g = S.GpuImpl(S.MEDIA[name], device=local)
+            for secondary in (False, True):  # camera rays (first scatter) and rays that carry Renewal state from a previous vertex
+                rr, ss = S.camera_rays(nq, seed=11, secondary=secondary)
+                r, s_ = g._rays_state(rr, ss)
+                out = g.m.sample_distance(r, s_, scene_seed=1, count_evals=True)
+                torch.cuda.synchronize()
+                r, s_ = g._rays_state(rr, ss)
+                a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                a.record(stream); out = g.m.sample_distance(r, s_, scene_seed=1, out=out, stream=stream); b.record(stream); torch.cuda.synchronize()
+                qs = a.elapsed_time(b) * 1e-3
+                ev = int(out["n_evals"].view(torch.int32).to(torch.int64).sum().item())
+                row = {"queries_per_s": nq / qs, "noise_evals_per_s": ev / qs, "evals_per_query": ev / nq}
+                if not secondary:
+                    extra[key] = dict({"workload": what + ", 2^20 camera rays, step 0.01"}, **row)
+                else:
+                    extra[key]["secondary"] = row
+            g.close()
         extra["medium_queries"]["kernel"] = "k_march (cached wavefront march)"
-        g = S.GpuImpl(S.MEDIA["c5_multires_nonstat_renewalplus"], device=local)
-        r, s = g._rays_state(rays, st)
-        out = g.m.sample_distance(r, s, scene_seed=1, count_evals=True)
-        torch.cuda.synchronize()
-        r, s = g._rays_state(rays, st)
-        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        a.record(stream); out = g.m.sample_distance(r, s, scene_seed=1, out=out, stream=stream); b.record(stream); torch.cuda.synchronize()
-        qs = a.elapsed_time(b) * 1e-3
-        ev = int(out["n_evals"].view(torch.int32).to(torch.int64).sum().item())
-        extra["medium_queries_c5"] = {"workload": "C5 medium (multi-resolution non-stationary, renewal+), 2^20 camera rays, step 0.01",
-                                      "queries_per_s": nq / qs, "noise_evals_per_s": ev / qs, "evals_per_query": ev / nq}
-        g.close()
 
     # ---- CPU baseline on this box's host cores (bounded sample)
     threads = os.cpu_count() or 1
@@ -341,6 +341,10 @@ def run_gpu(args):
             render["cpu_reference"] = {"camera_paths_per_s": ref_paths_s, "cores": threads, "seconds": ref_sec, "kind": "reference",
                                        "sample": "the same scene at 64x64 @4spp through the unmodified reference renderer (NEE on, scene_bvh off)"}
             render["speedup_vs_cpu_reference"] = render["camera_paths_per_s"] / ref_paths_s
+            ref_paths_s, ref_sec = cpu_reference_render(S.appendix_a_scene(S.c4_scene_medium(), 64, 16, quad=True), threads)
+            render_c4["cpu_reference"] = {"camera_paths_per_s": ref_paths_s, "cores": threads, "seconds": ref_sec, "kind": "reference",
+                                          "sample": "the same scene at 64x64 @16spp through the unmodified reference renderer"}
+            render_c4["speedup_vs_cpu_reference"] = render_c4["camera_paths_per_s"] / ref_paths_s
         except Exception as ex:  # the checker must never take the bench line down
             render["cpu_reference"] = {"unavailable": str(ex)[:200]}
     impl, kind = cpu_impl(mj, threads)
