@@ -15,7 +15,7 @@ ROOT = os.path.dirname(HERE)
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libscn_b200.so")
 SOURCES = ["scn_api.cu", "scn_render.cu", "scn_json.cpp", "scn_params.cpp"]
-HEADERS = ["scn_device.cuh", "scn_fast.cuh", "scn_march.cuh", "scn_internal.h", os.path.join("..", "..", "include", "scn.h"), os.path.join("..", "..", "include", "scn_render.h")]
+HEADERS = ["scn_device.cuh", "scn_fast.cuh", "scn_march.cuh", "scn_march1d.cuh", "scn_internal.h", os.path.join("..", "..", "include", "scn.h"), os.path.join("..", "..", "include", "scn_render.h")]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "-Xcompiler", "-fPIC,-O2", "-shared"]
 
 

@@ -15,6 +15,7 @@
 #include "scn_device.cuh"
 #include "scn_fast.cuh"
 #include "scn_march.cuh"
+#include "scn_march1d.cuh"
 #include <atomic>
 
 namespace scn {
@@ -181,6 +182,7 @@ struct scn_medium {
     mutable std::atomic<unsigned> next_counter{0};
     int sm_count = 0;
     int march_block = 0; // 128 / 64, 0 = generic kernels only
+    bool march1d = false; // 1D-sampling media covered by k_march1d (scn_march1d.cuh)
 };
 
 static inline unsigned grid_for(size_t n) { return (unsigned)((n + BLOCK - 1) / BLOCK); }
@@ -195,7 +197,7 @@ struct DeviceGuard {
 // cached wavefront march (scn_march.cuh) for the configurations it covers; SCN_FORCE_GENERIC=1 keeps the generic walk
 static bool use_march(const scn_medium *m) {
     static const bool forced = [] { const char *e = getenv("SCN_FORCE_GENERIC"); return e && e[0] == '1'; }();
-    return m->march_block != 0 && !forced;
+    return (m->march_block != 0 || m->march1d) && !forced;
 }
 template <bool TRANSMIT>
 static int launch_march(const scn_medium *m, const Rays &kr, const State &ks, const Samples &ko, float *T, uint32_t *n_evals, size_t n, cudaStream_t s) {
@@ -205,8 +207,8 @@ static int launch_march(const scn_medium *m, const Rays &kr, const State &ks, co
         if (b) { return set_error(SCN_EINVAL, "batches above 2^30 rays are not supported"); }
         A.counter = m->counters + (m->next_counter.fetch_add(1) % scn_medium::COUNTERS);
         SCN_CUDA(cudaMemsetAsync(A.counter, 0, sizeof(unsigned int), s));
-        cudaError_t e = launch_march_t<TRANSMIT>(m->P, A, m->march_block, m->sm_count, s);
-        if (e != cudaSuccess) return cuda_fail(e, "k_march");
+        cudaError_t e = m->march1d ? launch_march1d_t<TRANSMIT>(m->P, A, m->sm_count, s) : launch_march_t<TRANSMIT>(m->P, A, m->march_block, m->sm_count, s);
+        if (e != cudaSuccess) return cuda_fail(e, m->march1d ? "k_march1d" : "k_march");
     }
     return SCN_OK;
 }
@@ -233,11 +235,17 @@ int scn_medium_create(const scn_medium_desc *desc, int device, scn_medium **out)
     if (!m) return set_error(SCN_ENOMEM, "out of memory");
     m->desc = *desc; m->P = P; m->device = device;
     m->march_block = march_block_size(P);
+    m->march1d = march1d_supported(P);
     {
         DeviceGuard g(device);
         cudaError_t e1 = cudaDeviceGetAttribute(&m->sm_count, cudaDevAttrMultiProcessorCount, device);
         cudaError_t e2 = cudaMalloc((void **)&m->counters, scn_medium::COUNTERS * sizeof(unsigned int));
         if (e1 != cudaSuccess || e2 != cudaSuccess) { delete m; return cuda_fail(e1 != cudaSuccess ? e1 : e2, "scn_medium_create"); }
+        if (m->march1d) { // k_march1d's per-call scratch comes from the stream-ordered pool: keep freed blocks cached instead of returning them at every sync
+            cudaMemPool_t pool; unsigned long long keep = ~0ULL;
+            if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+            cudaGetLastError();
+        }
     }
     *out = m;
     return SCN_OK;
