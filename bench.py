@@ -58,15 +58,30 @@ class ClockSampler(threading.Thread):
 
     def run(self):
         q = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
-        while not self.stop_flag.is_set():
+        # one nvidia-smi process in loop mode (a sample every 20 ms) instead of one process per sample: the timed region is short
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + q, "--format=csv,noheader,nounits", "-lms", "20"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except Exception:
+            self.proc = None
+            return
+        for line in self.proc.stdout:
+            if self.stop_flag.is_set():
+                break
+            line = line.strip()
+            if line:
+                self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        self.stop_flag.set()
+        proc = getattr(self, "proc", None)
+        if proc is not None:
             try:
-                out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + q, "--format=csv,noheader,nounits"],
-                                     capture_output=True, text=True, timeout=5).stdout.strip()
-                if out:
-                    self.rows.append([x.strip() for x in out.split(",")])
+                proc.terminate()  # the exact process this sampler started
+                proc.wait(timeout=3)
             except Exception:
                 pass
-            self.stop_flag.wait(0.1)
+        self.join(timeout=3)
 
     def summary(self):
         sm = [float(r[0]) for r in self.rows if r and r[0].replace(".", "").isdigit()]
@@ -188,6 +203,8 @@ def run_gpu(args):
     torch.cuda.synchronize()
     sampler = ClockSampler(local)
     sampler.start()
+    time.sleep(0.15)  # let nvidia-smi come up; its first samples then fall inside the timed region
+    sampler.rows.clear()
     if world > 1:
         dist.barrier()
     torch.cuda.synchronize()
@@ -200,7 +217,7 @@ def run_gpu(args):
     if world > 1:
         dist.barrier()
     ms = e0.elapsed_time(e1)
-    sampler.stop_flag.set(); sampler.join(timeout=3)
+    sampler.stop()
     t = torch.tensor([ms], device=dev, dtype=torch.float64)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -235,7 +252,7 @@ def run_gpu(args):
         from sparse_conv_gpis_tungsten_b200 import render as R
 
         def timed_render(sc, spp, label):
-            wr = R.WavefrontRenderer(sc, device=local, rank=rank, world=world); wr.render(1); wr.close()  # warm-up
+            wr = R.WavefrontRenderer(sc, device=local, rank=rank, world=world); wr.render(1); R.gather_image_rgb(wr, world); wr.close()  # warm-up (kernels, NCCL all_gather connections)
             wr = R.WavefrontRenderer(sc, device=local, rank=rank, world=world)
             torch.cuda.synchronize()
             if world > 1:
@@ -392,7 +409,7 @@ class StdoutToStderr:
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--steps", type=int, default=40)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--points", type=int, default=N_POINTS)

@@ -286,8 +286,13 @@ def gather_image(renderer, world=1, channel=0):
         cap = (renderer.n_tiles + world - 1) // world
         pad = torch.zeros(cap, TILE, TILE, dtype=torch.float32, device=local.device)
         pad[: local.shape[0]] = local
-        out = [torch.empty_like(pad) for _ in range(world)]
-        dist.all_gather(out, pad)
+        if dist.get_backend() == "nccl":
+            flat = torch.empty(world * cap, TILE, TILE, dtype=torch.float32, device=local.device)
+            dist.all_gather_into_tensor(flat, pad)  # one NCCL all_gather straight into the assembled buffer
+            out = list(flat.view(world, cap, TILE, TILE).unbind(0))
+        else:
+            out = [torch.empty_like(pad) for _ in range(world)]
+            dist.all_gather(out, pad)
         parts = [out[r][: tile_range(renderer.n_tiles, r, world)[1]] for r in range(world)]
         tiles = torch.cat(parts, 0)
     else:
