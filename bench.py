@@ -247,13 +247,13 @@ def run_gpu(args):
 
     # ---- tile-sharded wavefront renders: every rank renders its contiguous tile range, one NCCL all_gather of the slices.
     #      C1 = Appendix A.1 without next-event estimation; C4 = Appendix A.3 (copper conductor phase bsdf, quad light, NEE + MIS)
-    render, render_c4 = None, None
+    render, render_c4, render_c5 = None, None, None
     if not args.no_extras:
         from sparse_conv_gpis_tungsten_b200 import render as R
 
-        def timed_render(sc, spp, label):
-            wr = R.WavefrontRenderer(sc, device=local, rank=rank, world=world); wr.render(1); R.gather_image_rgb(wr, world); wr.close()  # warm-up (kernels, NCCL all_gather connections)
-            wr = R.WavefrontRenderer(sc, device=local, rank=rank, world=world)
+        def timed_render(sc, spp, label, sharding="interleaved"):
+            wr = R.WavefrontRenderer(sc, device=local, rank=rank, world=world, sharding=sharding); wr.render(1); R.gather_image_rgb(wr, world); wr.close()  # warm-up (kernels, NCCL all_gather connections)
+            wr = R.WavefrontRenderer(sc, device=local, rank=rank, world=world, sharding=sharding)
             torch.cuda.synchronize()
             if world > 1:
                 dist.barrier()
@@ -263,13 +263,17 @@ def run_gpu(args):
             if world > 1:
                 dist.all_reduce(tr, op=dist.ReduceOp.MAX)
             res = sc["camera"]["resolution"]
-            out = {"workload": "%s %dx%d @%dspp, max_bounces %d, nee %s, 16x16 tiles sharded over %d GPU(s), one all_gather" % (label, res[0], res[1], spp, sc["integrator"]["max_bounces"], "on" if wr.nee else "off", world),
+            out = {"workload": "%s %dx%d @%dspp, max_bounces %d, nee %s, 16x16 tiles sharded over %d GPU(s) (%s), one all_gather" % (label, res[0], res[1], spp, sc["integrator"]["max_bounces"], "on" if wr.nee else "off", world, wr.sharding),
                    "ms": float(tr.item()), "camera_paths_per_s": res[0] * res[1] * spp / (float(tr.item()) * 1e-3), "mean_radiance": float(img.mean().item())}
             wr.close()
             return out
 
         render = timed_render(S.appendix_a_scene(S.MEDIA["c1_sphere_3d_none"], 512, 16), 16, "C1 scene (Appendix A.1)")
         render_c4 = timed_render(S.appendix_a_scene(S.c4_scene_medium(), 512, 16, quad=True), 16, "C4 scene (Appendix A.3: 1D Renewal+ XY, copper conductor, quad light, mis)")
+        render_c5 = timed_render(S.appendix_a_scene(S.MEDIA["c5_multires_nonstat_renewalplus"], 512, 16), 16, "C5 scene (Appendix A.4: multi-resolution non-stationary, renewal+)")
+        if world > 1:  # the contiguous ranges of SURVEY 8(e) next to the round-robin ownership used above
+            render["contiguous_ms"] = timed_render(S.appendix_a_scene(S.MEDIA["c1_sphere_3d_none"], 512, 16), 16, "C1", "contiguous")["ms"]
+            render_c5["contiguous_ms"] = timed_render(S.appendix_a_scene(S.MEDIA["c5_multires_nonstat_renewalplus"], 512, 16), 16, "C5", "contiguous")["ms"]
 
     if rank != 0:
         if world > 1:
@@ -309,6 +313,7 @@ def run_gpu(args):
     if render is not None:
         extra["render"] = render
         extra["render_c4"] = render_c4
+        extra["render_c5"] = render_c5
     if not args.no_extras:
         sweep = {}
         for iso in (True, False):

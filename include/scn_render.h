@@ -94,6 +94,12 @@ uint32_t scn_wf_tile_count(uint32_t res_x, uint32_t res_y);
 int scn_wf_raygen(const scn_wf_scene *scene, const scn_medium *m, uint32_t tile_first, uint32_t tile_count, uint32_t spp_first, uint32_t spp_count,
                   const scn_wf_paths *paths, size_t n, void *stream);
 
+/* The same for tiles tile_first + k * tile_stride, k in [0, tile_count): round-robin tile ownership across GPUs (SURVEY.md 8(e):
+ * interleaved ranges balance the load when contiguous ranges leave some GPUs with background-only tiles).
+ * local_pixel = k * 256 + in-tile offset. */
+int scn_wf_raygen_strided(const scn_wf_scene *scene, const scn_medium *m, uint32_t tile_first, uint32_t tile_stride, uint32_t tile_count,
+                          uint32_t spp_first, uint32_t spp_count, const scn_wf_paths *paths, size_t n, void *stream);
+
 /* After scn_sample_distance_batch on the wavefront: terminate / scatter every path (PathTracer.cpp:69-169 restricted as above)
  * and write the next bounce's rays in place.  `bounce` is the index of the bounce just queried. */
 int scn_wf_shade(const scn_wf_scene *scene, const scn_medium *m, const scn_wf_paths *paths, size_t n, int32_t bounce, uint32_t spp_first, uint32_t spp_count,

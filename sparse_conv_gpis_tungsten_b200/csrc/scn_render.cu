@@ -109,12 +109,12 @@ __device__ __forceinline__ f3 wf_specular_weight(const scn_wf_scene &S, float co
 __device__ __forceinline__ float power_heuristic(float a, float b) { return (a * a) / (a * a + b * b); }
 
 // PathTracer::traceSample :31-59 — camera sample, first intersection with the scene (the cube), medium state reset
-__global__ void __launch_bounds__(WF_BLOCK) k_wf_raygen(const scn_wf_scene S, const WfPaths W, uint32_t tile_first, uint32_t spp_first, uint32_t spp_count, size_t n) {
+__global__ void __launch_bounds__(WF_BLOCK) k_wf_raygen(const scn_wf_scene S, const WfPaths W, uint32_t tile_first, uint32_t tile_stride, uint32_t spp_first, uint32_t spp_count, size_t n) {
     const size_t i = (size_t)blockIdx.x * WF_BLOCK + threadIdx.x;
     if (i >= n) return;
     const uint32_t s = (uint32_t)(i % spp_count); const size_t lp = i / spp_count;
     const uint32_t tiles_x = (S.res_x + SCN_WF_TILE - 1) / SCN_WF_TILE;
-    const uint32_t tile = tile_first + (uint32_t)(lp / (SCN_WF_TILE * SCN_WF_TILE)), in_tile = (uint32_t)(lp % (SCN_WF_TILE * SCN_WF_TILE));
+    const uint32_t tile = tile_first + tile_stride * (uint32_t)(lp / (SCN_WF_TILE * SCN_WF_TILE)), in_tile = (uint32_t)(lp % (SCN_WF_TILE * SCN_WF_TILE));
     const uint32_t x = (tile % tiles_x) * SCN_WF_TILE + in_tile % SCN_WF_TILE, y = (tile / tiles_x) * SCN_WF_TILE + in_tile / SCN_WF_TILE;
     const uint32_t spp = spp_first + s;
     // state.reset() (media/Medium.hpp:70-80) and RayInfo
@@ -456,17 +456,24 @@ extern "C" {
 
 uint32_t scn_wf_tile_count(uint32_t res_x, uint32_t res_y) { return ((res_x + SCN_WF_TILE - 1) / SCN_WF_TILE) * ((res_y + SCN_WF_TILE - 1) / SCN_WF_TILE); }
 
-int scn_wf_raygen(const scn_wf_scene *scene, const scn_medium *m, uint32_t tile_first, uint32_t tile_count, uint32_t spp_first, uint32_t spp_count,
-                  const scn_wf_paths *paths, size_t n, void *stream) {
+int scn_wf_raygen_strided(const scn_wf_scene *scene, const scn_medium *m, uint32_t tile_first, uint32_t tile_stride, uint32_t tile_count, uint32_t spp_first,
+                          uint32_t spp_count, const scn_wf_paths *paths, size_t n, void *stream) {
     (void)m;
     if (!scene || !paths) return set_error(SCN_EINVAL, "null argument");
     if (spp_count == 0 || n != (size_t)tile_count * SCN_WF_TILE * SCN_WF_TILE * spp_count) return set_error(SCN_EINVAL, "raygen: n must be tile_count * 256 * spp_count");
-    if (tile_first + tile_count > scn_wf_tile_count(scene->res_x, scene->res_y)) return set_error(SCN_EINVAL, "raygen: tile range outside the image");
+    if (tile_stride == 0) return set_error(SCN_EINVAL, "raygen: tile_stride must be >= 1");
+    if (tile_count && (uint64_t)tile_first + (uint64_t)tile_stride * (tile_count - 1) >= scn_wf_tile_count(scene->res_x, scene->res_y))
+        return set_error(SCN_EINVAL, "raygen: tile range outside the image");
     if (n == 0) return SCN_OK;
     WfPaths W; if (int rc = wf_paths(paths, W, false)) return rc;
     if (scene->nee) if (int rc = wf_nee_arrays(paths)) return rc;
-    k_wf_raygen<<<(unsigned)((n + WF_BLOCK - 1) / WF_BLOCK), WF_BLOCK, 0, (cudaStream_t)stream>>>(*scene, W, tile_first, spp_first, spp_count, n);
+    k_wf_raygen<<<(unsigned)((n + WF_BLOCK - 1) / WF_BLOCK), WF_BLOCK, 0, (cudaStream_t)stream>>>(*scene, W, tile_first, tile_stride, spp_first, spp_count, n);
     return wf_check("k_wf_raygen");
+}
+
+int scn_wf_raygen(const scn_wf_scene *scene, const scn_medium *m, uint32_t tile_first, uint32_t tile_count, uint32_t spp_first, uint32_t spp_count,
+                  const scn_wf_paths *paths, size_t n, void *stream) {
+    return scn_wf_raygen_strided(scene, m, tile_first, 1u, tile_count, spp_first, spp_count, paths, n, stream);
 }
 
 int scn_wf_shade(const scn_wf_scene *scene, const scn_medium *m, const scn_wf_paths *paths, size_t n, int32_t bounce, uint32_t spp_first, uint32_t spp_count,

@@ -44,6 +44,8 @@ COMPLEX_IOR = {"Cu": ((0.2004376970, 0.9240334304, 1.1022119527), (3.9129485033,
 RENDER_SYMBOLS = {
     "scn_wf_tile_count": (C.c_uint32, [C.c_uint32, C.c_uint32]),
     "scn_wf_raygen": (C.c_int, [C.POINTER(WfScene), abi.MediumP, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.POINTER(WfPaths), C.c_size_t, C.c_void_p]),
+    "scn_wf_raygen_strided": (C.c_int, [C.POINTER(WfScene), abi.MediumP, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.POINTER(WfPaths), C.c_size_t,
+                                        C.c_void_p]),
     "scn_wf_shade": (C.c_int, [C.POINTER(WfScene), abi.MediumP, C.POINTER(WfPaths), C.c_size_t, C.c_int32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p]),
     "scn_wf_accumulate": (C.c_int, [abi.f32p, abi.f32p, C.c_size_t, C.c_uint32, C.c_void_p]),
     "scn_wf_nee_setup": (C.c_int, [C.POINTER(WfScene), abi.MediumP, C.POINTER(WfPaths), C.POINTER(WfShadow), C.POINTER(WfShadow), C.c_size_t, C.c_int32, C.c_void_p]),
@@ -143,10 +145,21 @@ def tile_range(n_tiles, rank, world):
     return first, base + (1 if rank < rem else 0)
 
 
-class WavefrontRenderer:
-    """One GPU's share of a render: tiles [tile_first, tile_first + tile_count)."""
+def tile_set(n_tiles, rank, world, sharding="contiguous"):
+    """(tile_first, tile_stride, tile_count) of a rank.  "contiguous" is `tile_range`; "interleaved" deals the tiles round-robin
+    (rank, rank + world, ...), which SURVEY.md §8(e) asks for when contiguous ranges leave some GPUs with background-only tiles."""
+    if sharding == "contiguous" or world == 1:
+        first, count = tile_range(n_tiles, rank, world)
+        return first, 1, count
+    if sharding != "interleaved":
+        raise ValueError("sharding must be 'contiguous' or 'interleaved'")
+    return rank, world, (n_tiles - rank + world - 1) // world if rank < n_tiles else 0
 
-    def __init__(self, scene_json, device=0, rank=0, world=1, max_paths=1 << 22, nee=None):
+
+class WavefrontRenderer:
+    """One GPU's share of a render: tiles tile_first + k * tile_stride, k < tile_count."""
+
+    def __init__(self, scene_json, device=0, rank=0, world=1, max_paths=1 << 22, nee=None, sharding="contiguous"):
         self.lib = load()
         self.scene = scene_from_json(scene_json)
         if nee is not None:
@@ -155,7 +168,8 @@ class WavefrontRenderer:
         self.dev = torch.device("cuda", device)
         self.medium = SparseConvolutionNoiseMedium.from_json(scene_json["media"][0], device)
         self.n_tiles = int(self.lib.scn_wf_tile_count(self.scene.res_x, self.scene.res_y))
-        self.tile_first, self.tile_count = tile_range(self.n_tiles, rank, world)
+        self.sharding = sharding if world > 1 else "contiguous"
+        self.tile_first, self.tile_stride, self.tile_count = tile_set(self.n_tiles, rank, world, self.sharding)
         self.n_pixels = self.tile_count * TILE * TILE
         self.max_paths = max_paths
         self.framebuffer = torch.zeros(max(self.n_pixels, 1), dtype=torch.float32, device=self.dev)  # red (or grey) plane
@@ -230,7 +244,8 @@ class WavefrontRenderer:
             c = min(chunk, spp - done)
             n = self.n_pixels * c
             self._alloc(n)
-            abi.check(self.lib.scn_wf_raygen(C.byref(self.scene), self.medium._h, self.tile_first, self.tile_count, self.spp_done + done, c, C.byref(self.paths), n, sp))
+            abi.check(self.lib.scn_wf_raygen_strided(C.byref(self.scene), self.medium._h, self.tile_first, self.tile_stride, self.tile_count, self.spp_done + done, c,
+                                                     C.byref(self.paths), n, sp))
             for bounce in range(self.scene.max_bounces):
                 if count_queries:
                     self.queries += int(self.alive.sum().item())
@@ -293,8 +308,11 @@ def gather_image(renderer, world=1, channel=0):
         else:
             out = [torch.empty_like(pad) for _ in range(world)]
             dist.all_gather(out, pad)
-        parts = [out[r][: tile_range(renderer.n_tiles, r, world)[1]] for r in range(world)]
-        tiles = torch.cat(parts, 0)
+        if getattr(renderer, "sharding", "contiguous") == "interleaved":  # tile t lives at out[t % world][t // world]
+            tiles = torch.stack(out, 1).reshape(world * cap, TILE, TILE)[: renderer.n_tiles]
+        else:
+            parts = [out[r][: tile_range(renderer.n_tiles, r, world)[1]] for r in range(world)]
+            tiles = torch.cat(parts, 0)
     else:
         tiles = local
     return assemble_image(tiles, renderer.scene.res_x, renderer.scene.res_y)

@@ -29,6 +29,12 @@ def test_tile_partition_and_assembly():
             assert rs[0][0] == 0 and sum(c for _, c in rs) == n_tiles
             assert all(rs[i][0] + rs[i][1] == rs[i + 1][0] for i in range(world - 1))  # contiguous, in order
             assert max(c for _, c in rs) - min(c for _, c in rs) <= 1
+            assert [R.tile_set(n_tiles, r, world, "contiguous") for r in range(world)] == [(f, 1, c) for f, c in rs]
+            # round-robin ownership: every tile exactly once, counts within one of each other
+            sets = [R.tile_set(n_tiles, r, world, "interleaved") for r in range(world)]
+            owned = sorted(f + k * st for f, st, c in sets for k in range(c))
+            assert owned == list(range(n_tiles))
+            assert max(c for _, _, c in sets) - min(c for _, _, c in sets) <= 1
     # tiles in diceTiles order (row-major over the tile grid) -> image, edge tiles cropped
     rx, ry = 40, 24
     tx, ty = 3, 2
@@ -74,12 +80,14 @@ rank, world = dist.get_rank(), dist.get_world_size()
 class Fake:  # the fields gather_image reads
     pass
 f = Fake(); f.n_tiles = 7; f.scene = Fake(); f.scene.res_x, f.scene.res_y = 100, 16
-first, count = R.tile_range(f.n_tiles, rank, world)
-f.local_image = lambda: (torch.arange(first, first + count, dtype=torch.float32)[:, None, None] + torch.zeros(count, 16, 16))
-img = R.gather_image(f, world)
-assert img.shape == (16, 100)
 want = (torch.arange(100) // 16).float()[None, :].expand(16, 100)
-assert torch.equal(img, want), rank
+for sharding in ("contiguous", "interleaved"):
+    first, stride, count = R.tile_set(f.n_tiles, rank, world, sharding)
+    f.sharding = sharding
+    f.local_image = lambda: ((first + stride * torch.arange(count)).float()[:, None, None] + torch.zeros(count, 16, 16))
+    img = R.gather_image(f, world)
+    assert img.shape == (16, 100)
+    assert torch.equal(img, want), (rank, sharding)
 dist.destroy_process_group()
 print("ok", rank)
 ''' % S.ROOT)
@@ -118,7 +126,12 @@ def test_wavefront_stage_vs_restatement():
     a.render(4); b.render(4)
     both = R.assemble_image(torch.cat([a.local_image(), b.local_image()], 0), 40, 24)
     assert torch.equal(both, R.gather_image(r, 1))
-    for x in (r, r2, a, b):
+    # round-robin tile ownership (scn_wf_raygen_strided): tile t of the image is local tile t // 2 of rank t % 2
+    ia, ib = (R.WavefrontRenderer(SCENE, device=0, rank=k, world=2, sharding="interleaved") for k in range(2))
+    ia.render(4); ib.render(4)
+    tiles = torch.stack([ia.local_image(), ib.local_image()], 1).reshape(-1, 16, 16)[: r.n_tiles]
+    assert torch.equal(R.assemble_image(tiles, 40, 24), R.gather_image(r, 1))
+    for x in (r, r2, a, b, ia, ib):
         x.close()
 
 
