@@ -203,7 +203,7 @@ template <bool TRANSMIT>
 static int launch_march(const scn_medium *m, const Rays &kr, const State &ks, const Samples &ko, float *T, uint32_t *n_evals, size_t n, cudaStream_t s) {
     for (size_t b = 0; b < n; b += 0x40000000u) { // the ray counter is 32 bits wide
         unsigned c = (unsigned)(n - b < 0x40000000u ? n - b : 0x40000000u);
-        MarchArgs A; A.r = kr; A.s = ks; A.o = ko; A.T = T; A.n_evals = n_evals; A.n = c; A.K = march_cache_entries(m->P.n_imp);
+        MarchArgs A; A.r = kr; A.s = ks; A.o = ko; A.T = T; A.n_evals = n_evals; A.n = c; A.K = march_cache_entries(m->P.n_imp, m->P.iso3d != 0);
         if (b) { return set_error(SCN_EINVAL, "batches above 2^30 rays are not supported"); }
         A.counter = m->counters + (m->next_counter.fetch_add(1) % scn_medium::COUNTERS);
         SCN_CUDA(cudaMemsetAsync(A.counter, 0, sizeof(unsigned int), s));
