@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define SCN_ABI_VERSION 2
+#define SCN_ABI_VERSION 3
 
 /* error codes */
 #define SCN_OK 0
@@ -135,6 +135,11 @@ typedef struct scn_medium_desc {
     float gabor_a_inv;                /* "a_inv"                   default 1          */
     float gabor_f_inv;                /* "f_inv"                   default 1          */
     float gabor_omega[3];             /* "omega" (normalised at parse time; the reference leaves it uninitialised when absent) */
+    /* proc_nonstationary rotation anisotropy (appended in ABI version 3): "aniso" scalar field, angle = field(p) * pi/2 about z,
+     * axis scales (1.5, 1/1.5, 1) hard-coded in the reference (math/GPFunctions.cpp:1678-1690, GPFunctions.hpp:2372).
+     * 3D sampling only: the 1D path reads StationaryCovariance::_local_to_world, whose off-diagonal is never initialised. */
+    int32_t _pad1;
+    scn_field_desc aniso_field;
 } scn_medium_desc;
 
 typedef struct scn_medium scn_medium; /* opaque; replaces the SparseConvolutionNoiseMedium object */

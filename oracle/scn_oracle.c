@@ -26,6 +26,7 @@ typedef struct { float x, y, z, w; } v4;
 typedef struct { double x, y, z; } d3;
 typedef struct { v3 n, t, b; } frame_t;
 
+#define ANISO_ON_AXIS 1.5f /* ProceduralNonstationaryCovariance::_anisotropyOnAxis, GPF.hpp:2372 */
 static __thread char g_err[256];
 static __thread uint64_t g_eval_count;
 const char *orc_last_error(void) { return g_err; }
@@ -140,6 +141,7 @@ struct orc_medium {
     int absorption_only;
     int kernel;              /* SCN_COV_SQUARED_EXPONENTIAL | SCN_COV_MATERN | SCN_COV_GABOR_ANISO | SCN_COV_GABOR_ISO */
     float k_a, k_f; v3 k_omega; /* Gabor: _a, _f, _omega (GPF:1087-1097) */
+    int has_aniso;           /* proc_nonstationary "aniso" field: rotation anisotropy of the splat kernel (GPF:1678-1690) */
 };
 
 orc_medium *orc_medium_create(const scn_medium_desc *desc) {
@@ -158,6 +160,8 @@ orc_medium *orc_medium_create(const scn_medium_desc *desc) {
         m->k_omega = V3(desc->gabor_omega[0], desc->gabor_omega[1], desc->gabor_omega[2]);
     }
     m->multires = !m->stationary && desc->multires;
+    m->has_aniso = !m->stationary && desc->aniso_field.type != SCN_FIELD_NONE;
+    if (m->has_aniso && desc->sampling_1d) { snprintf(g_err, sizeof g_err, "proc_nonstationary \"aniso\": 3D sampling only"); free(m); return NULL; }
     m->l_conv = desc->length_scale * sqrtf(2.f) / 2;
     m->l_aniso = V3(m->l_conv * desc->aniso[0], m->l_conv * desc->aniso[1], m->l_conv * desc->aniso[2]);
     m->l_aniso_inv = V3(1.0f / m->l_aniso.x, 1.0f / m->l_aniso.y, 1.0f / m->l_aniso.z);
@@ -229,7 +233,7 @@ static float cov_amplitude(const orc_medium *m, v3 p) {
 }
 /* splattingKernelRadius (GPF:696-709, 1245-1249) */
 static float cov_radius(const orc_medium *m, int is_identity, float local_scale) {
-    if (!m->stationary) { local_scale *= m->multires ? 1.0 : m->ls_max; local_scale *= 1.f; }
+    if (!m->stationary) { local_scale *= m->multires ? 1.0 : m->ls_max; local_scale *= m->has_aniso ? ANISO_ON_AXIS : 1.f; } /* max(a, 1/a), GPF:1741-1745 */
     float sf = m->d.kernel_scale;
     if (m->kernel == SCN_COV_MATERN) { /* GPF:1020-1025 */
         if (is_identity) return sf;
@@ -328,6 +332,29 @@ static float cov_splat_cov1d(const orc_medium *m, v3 pq, v3 pc) {
     return sqrtf(scale);
 }
 
+/* Eigen's fixed-size 3x3 inverse (cofactor form) */
+static void mat3_inverse(const float a[9], float r[9]);
+/* getNonstationaryAniso3D (GPF:1678-1690) with compute_ansio_full (GPF:26-39): G = (S V)^T (S V), V = rotation by angle about z,
+ * S = diag(a, 1/a, 1), a = _anisotropyOnAxis = 1.5 (GPF.hpp:2372); row-major.  Returns 0 without an anisotropy field. */
+static int cov_aniso3d(const orc_medium *m, v3 p_world, float G[9]) {
+    if (!m->has_aniso) return 0;
+    float angle = (float)(field_scalar(&m->d.aniso_field, to_d3(p_world)) * (3.1415926536f * 0.5f));
+    float c = cosf(angle), sn = sinf(angle);
+    float ax[3] = {ANISO_ON_AXIS, 1.f / ANISO_ON_AXIS, 1.f};
+    float V[9] = {c, sn, 0.f, -sn, c, 0.f, 0.f, 0.f, 1.f}, M[9];
+    for (int i = 0; i < 3; ++i) for (int j = 0; j < 3; ++j) M[i * 3 + j] = ax[i] * V[i * 3 + j];
+    /* Eigen's unrolled three-term reduction is x0 + (x1 + x2) (redux_novec_unroller splits in halves) */
+    for (int i = 0; i < 3; ++i) for (int j = 0; j < 3; ++j) G[i * 3 + j] = M[0 * 3 + i] * M[0 * 3 + j] + (M[1 * 3 + i] * M[1 * 3 + j] + M[2 * 3 + i] * M[2 * 3 + j]);
+    return 1;
+}
+/* getInvCovMtx with an anisotropy matrix (GPF:774-802): invSigma^T aniso_inv invSigma, then the isCov / localScale / 0.5 factors */
+static void se_inv_cov_full(const orc_medium *m, const float aniso_inv[9], int is_cov, int is_iso, float gs, float ls, float M[9]) {
+    float sg[3] = {1.f, 1.f, 1.f};
+    if (!is_iso) { sg[0] = m->l_aniso_inv.x / gs; sg[1] = m->l_aniso_inv.y / gs; sg[2] = m->l_aniso_inv.z / gs; }
+    for (int i = 0; i < 3; ++i) for (int j = 0; j < 3; ++j) M[i * 3 + j] = (sg[i] * aniso_inv[i * 3 + j]) * sg[j];
+    for (int i = 0; i < 9; ++i) { if (is_cov) M[i] *= 0.5f; M[i] /= sqrf(ls); M[i] *= 0.5f; }
+}
+
 /* getInvCovMtx diagonal (GPF:774-802) */
 static v3 se_inv_cov_diag(const orc_medium *m, int is_cov, int is_iso, float gs, float ls) {
     v3 d = V3(1.f, 1.f, 1.f);
@@ -345,6 +372,14 @@ static v4 cov_kernel3d(const orc_medium *m, v3 pa, v3 pb, int is_cov, int is_iso
     float ls = cov_ns_scale(m, p_world);
     v3 ab = v3_sub(pa, pb);
     if (m->kernel != SCN_COV_SQUARED_EXPONENTIAL) return alt_kernel3d(m, ab);
+    float G[9];
+    if (cov_aniso3d(m, p_world, G)) { /* GPF:556-558: aniso_inv = inverse, full matrix */
+        float Gi[9], Mf[9]; mat3_inverse(G, Gi); se_inv_cov_full(m, Gi, is_cov, is_iso, gs, ls, Mf);
+        /* dist2_ab = (ab^T M) ab and ab . M.col(j) (GPF.hpp:76-78, GPF:804-817), three-term sums as x0 + (x1 + x2) */
+        v3 Mab = V3(ab.x * Mf[0] + (ab.y * Mf[3] + ab.z * Mf[6]), ab.x * Mf[1] + (ab.y * Mf[4] + ab.z * Mf[7]), ab.x * Mf[2] + (ab.y * Mf[5] + ab.z * Mf[8]));
+        float f = expf(-(Mab.x * ab.x + (Mab.y * ab.y + Mab.z * ab.z)));
+        return V4(f, -2.f * Mab.x * f, -2.f * Mab.y * f, -2.f * Mab.z * f);
+    }
     v3 M = se_inv_cov_diag(m, is_cov, is_iso, gs, ls);
     float absq = (ab.x * M.x) * ab.x + ((ab.y * M.y) * ab.y + (ab.z * M.z) * ab.z);
     float f = expf(-absq);
@@ -354,6 +389,19 @@ static v4 cov_kernel3d(const orc_medium *m, v3 pa, v3 pb, int is_cov, int is_iso
 static v4 cov_kernel3d_grad(const orc_medium *m, v3 pa, v3 pb, v3 c, int is_cov, int is_iso, float gs, v3 p_world) {
     float ls = cov_ns_scale(m, p_world);
     v3 ab = v3_sub(pa, pb);
+    float G[9];
+    if (cov_aniso3d(m, p_world, G)) { /* GPF:565-577, 819-833 with the full matrix */
+        float Gi[9], Mf[9]; mat3_inverse(G, Gi); se_inv_cov_full(m, Gi, is_cov, is_iso, gs, ls, Mf);
+        /* dist2_ab = (ab^T M) ab and ab . M.col(j) (GPF.hpp:76-78, GPF:804-817), three-term sums as x0 + (x1 + x2) */
+        v3 Mab = V3(ab.x * Mf[0] + (ab.y * Mf[3] + ab.z * Mf[6]), ab.x * Mf[1] + (ab.y * Mf[4] + ab.z * Mf[7]), ab.x * Mf[2] + (ab.y * Mf[5] + ab.z * Mf[8]));
+        float f = expf(-(Mab.x * ab.x + (Mab.y * ab.y + Mab.z * ab.z)));
+        float d[3] = {-2.f * Mab.x, -2.f * Mab.y, -2.f * Mab.z}, cc[3] = {c.x, c.y, c.z}, out[4] = {0.f, 0.f, 0.f, 0.f};
+        for (int i = 0; i < 3; ++i) {
+            out[0] += d[i] * f * cc[i];
+            for (int j = 0; j < 3; ++j) out[1 + j] += (d[i] * d[j] - 2.f * Mf[i * 3 + j]) * f * cc[i];
+        }
+        return V4(out[0], out[1], out[2], out[3]);
+    }
     v3 M = se_inv_cov_diag(m, is_cov, is_iso, gs, ls);
     float absq = (ab.x * M.x) * ab.x + ((ab.y * M.y) * ab.y + (ab.z * M.z) * ab.z);
     float f = expf(-absq);
@@ -705,6 +753,18 @@ static v3 cov_one_over_second_derivative_diag(const orc_medium *m, int is_iso) {
     return V3(r[0], r[4], r[8]);
 }
 
+/* sparseConvNoiseOneOverSecondDerivative with the anisotropy field (GPF:1239-1243, 713-739): (-2 * 0.25 * invSigma^T G^-1 invSigma)^-1 applied to v */
+static v3 cov_one_over_second_derivative_apply(const orc_medium *m, v3 p_world, int is_iso, v3 v) {
+    float G[9];
+    if (!cov_aniso3d(m, p_world, G)) return v3_mul(cov_one_over_second_derivative_diag(m, is_iso), v);
+    float Gi[9], a[9], r[9]; mat3_inverse(G, Gi);
+    float sg[3] = {1.f, 1.f, 1.f};
+    if (!is_iso) { sg[0] = m->l_aniso_inv.x; sg[1] = m->l_aniso_inv.y; sg[2] = m->l_aniso_inv.z; }
+    for (int i = 0; i < 3; ++i) for (int j = 0; j < 3; ++j) a[i * 3 + j] = -2.f * (((sg[i] * Gi[i * 3 + j]) * sg[j]) * 0.25f);
+    mat3_inverse(a, r);
+    return V3(r[0] * v.x + (r[1] * v.y + r[2] * v.z), r[3] * v.x + (r[4] * v.y + r[5] * v.z), r[6] * v.x + (r[7] * v.y + r[8] * v.z));
+}
+
 /* conditioning3D (SCN:441-517); the reference's sanity re-evaluations only print and are left out */
 static void real_conditioning3d(real_t *r, v3 p, v3 dir, float target_val, v3 target_grad, const info_t *info) {
     const orc_medium *m = r->m; int ctx = m->d.correlation_context;
@@ -732,11 +792,11 @@ static void real_conditioning3d(real_t *r, v3 p, v3 dir, float target_val, v3 ta
             v3 dir_iso = v3_normalized(cov_pos_w2l(m, dir, 1.0f));
             frame_t fr = frame_make(dir_iso);
             gs = frame_to_local(&fr, gs);
-            r->c3.gradient_scale = v3_mul(cov_one_over_second_derivative_diag(m, 1), gs);
+            r->c3.gradient_scale = cov_one_over_second_derivative_apply(m, p, 1, gs);
             if (m->multires) r->c3.gradient_scale = v3_div(r->c3.gradient_scale, ksi.z / ksi.x + ksi.w / ksi.y);
             else r->c3.gradient_scale = v3_scale(r->c3.gradient_scale, sqrf(cov_ns_scale(m, p)));
         } else {
-            r->c3.gradient_scale = v3_mul(cov_one_over_second_derivative_diag(m, 0), delta);
+            r->c3.gradient_scale = cov_one_over_second_derivative_apply(m, p, 0, delta);
             if (m->multires) r->c3.gradient_scale = v3_div(r->c3.gradient_scale, ksi.z / (ksi.x * ksi.x) + ksi.w / (ksi.y * ksi.y));
             else r->c3.gradient_scale = v3_scale(r->c3.gradient_scale, sqrf(cov_lateral_scale(m, p)));
         }

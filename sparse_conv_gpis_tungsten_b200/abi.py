@@ -39,7 +39,8 @@ class MediumDesc(C.Structure):
                 ("cov_type", C.c_int32), ("use_aniso_mtx", C.c_int32), ("sigma", C.c_float), ("length_scale", C.c_float), ("aniso", C.c_float * 3),
                 ("kernel_scale", C.c_float), ("aniso_mtx", C.c_float * 9),
                 ("multires", C.c_int32), ("ls", FieldDesc), ("var", FieldDesc),
-                ("matern_v", C.c_float), ("gabor_a_inv", C.c_float), ("gabor_f_inv", C.c_float), ("gabor_omega", C.c_float * 3)]
+                ("matern_v", C.c_float), ("gabor_a_inv", C.c_float), ("gabor_f_inv", C.c_float), ("gabor_omega", C.c_float * 3),
+                ("_pad1", C.c_int32), ("aniso_field", FieldDesc)]
 
 
 class Rays(C.Structure):
@@ -117,7 +118,7 @@ def load():
         fn = getattr(lib, name)  # AttributeError if the symbol is not exported
         fn.restype = res
         fn.argtypes = args
-    if lib.scn_abi_version() != 2:
+    if lib.scn_abi_version() != 3:
         raise ImportError("libscn_b200.so ABI version mismatch")
     _lib = lib
     return lib

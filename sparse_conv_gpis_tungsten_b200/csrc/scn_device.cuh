@@ -208,6 +208,61 @@ SCN_HD f4 se_kernel3d_grad(f3 ab, f3 M, f3 c) {
     return F4((dx * f) * c.x + (dy * f) * c.y + (dz * f) * c.z,
               h00 * c.x + h01 * c.y + h02 * c.z, h01 * c.x + h11 * c.y + h12 * c.z, h02 * c.x + h12 * c.y + h22 * c.z);
 }
+// ---------------------------------------------------------------- rotation-anisotropic non-stationary kernel (GPF:1678-1690)
+// 3x3 inverse in cofactor form (Eigen's fixed-size path), row-major
+SCN_HD void mat3_inverse(const float a[9], float r[9]) {
+#define SCN_A(i, j) a[((i) % 3) * 3 + ((j) % 3)]
+#define SCN_COF(i, j) (SCN_A(i + 1, j + 1) * SCN_A(i + 2, j + 2) - SCN_A(i + 1, j + 2) * SCN_A(i + 2, j + 1))
+    float c00 = SCN_COF(0, 0), c10 = SCN_COF(1, 0), c20 = SCN_COF(2, 0);
+    float inv = 1.0f / (c00 * a[0] + (c10 * a[3] + c20 * a[6]));
+    r[0] = c00 * inv; r[1] = c10 * inv; r[2] = c20 * inv;
+    r[3] = SCN_COF(0, 1) * inv; r[4] = SCN_COF(1, 1) * inv; r[5] = SCN_COF(2, 1) * inv;
+    r[6] = SCN_COF(0, 2) * inv; r[7] = SCN_COF(1, 2) * inv; r[8] = SCN_COF(2, 2) * inv;
+#undef SCN_COF
+#undef SCN_A
+}
+// getNonstationaryAniso3D with compute_ansio_full (GPF:26-39): G = (S V)^T (S V), V = rotation by field(p) * pi/2 about z,
+// S = diag(1.5, 1/1.5, 1) (_anisotropyOnAxis, GPF.hpp:2372); row-major
+SCN_FN void cov_aniso3d(const Params &P, f3 p_world, float G[9]) {
+    const float angle = (float)(field_scalar(P.aniso_f, to_dbl3(p_world)) * (double)(3.1415926536f * 0.5f));
+    const float c = cosf(angle), sn = sinf(angle);
+    const float ax[3] = {1.5f, 1.f / 1.5f, 1.f};
+    const float V[9] = {c, sn, 0.f, -sn, c, 0.f, 0.f, 0.f, 1.f};
+    float M[9];
+    for (int i = 0; i < 3; ++i) for (int j = 0; j < 3; ++j) M[i * 3 + j] = ax[i] * V[i * 3 + j];
+    for (int i = 0; i < 3; ++i) for (int j = 0; j < 3; ++j) G[i * 3 + j] = M[i] * M[j] + (M[3 + i] * M[3 + j] + M[6 + i] * M[6 + j]); // Eigen's x0 + (x1 + x2)
+}
+// The splat kernel's inverse covariance at a query point: diagonal (d) or, with the anisotropy field, the full matrix
+// invSigma^T G^-1 invSigma with the isCov / localScale / 0.5 factors of getInvCovMtx (GPF:774-802)
+struct KMat { bool full; f3 d; float m[9]; };
+SCN_FN KMat kmat_make(const Params &P, f3 p_world, int is_cov, int is_iso, float gs, float ls) {
+    KMat K; K.full = P.has_aniso != 0; K.d = F3(0.f, 0.f, 0.f);
+    if (!K.full) { K.d = se_inv_cov_diag(P, is_cov, is_iso, gs, ls); return K; }
+    float G[9], Gi[9]; cov_aniso3d(P, p_world, G); mat3_inverse(G, Gi);
+    float sg[3] = {1.f, 1.f, 1.f};
+    if (!is_iso) { sg[0] = P.l_aniso_inv[0] / gs; sg[1] = P.l_aniso_inv[1] / gs; sg[2] = P.l_aniso_inv[2] / gs; }
+    const float k = (is_cov ? 0.5f : 1.0f), l2 = ls * ls;
+    for (int i = 0; i < 3; ++i) for (int j = 0; j < 3; ++j) K.m[i * 3 + j] = (sg[i] * Gi[i * 3 + j]) * sg[j] * k / l2 * 0.5f;
+    return K;
+}
+SCN_HD f4 se_kernel3d(f3 ab, const KMat &K) {
+    if (!K.full) return se_kernel3d(ab, K.d);
+    const f3 Mab = F3(ab.x * K.m[0] + (ab.y * K.m[3] + ab.z * K.m[6]), ab.x * K.m[1] + (ab.y * K.m[4] + ab.z * K.m[7]), ab.x * K.m[2] + (ab.y * K.m[5] + ab.z * K.m[8]));
+    const float f = fast_exp(-(ab.x * Mab.x + (ab.y * Mab.y + ab.z * Mab.z))), m2f = -2.f * f;
+    return F4(f, Mab.x * m2f, Mab.y * m2f, Mab.z * m2f);
+}
+SCN_HD f4 se_kernel3d_grad(f3 ab, const KMat &K, f3 c) {
+    if (!K.full) return se_kernel3d_grad(ab, K.d, c);
+    const f3 Mab = F3(ab.x * K.m[0] + (ab.y * K.m[3] + ab.z * K.m[6]), ab.x * K.m[1] + (ab.y * K.m[4] + ab.z * K.m[7]), ab.x * K.m[2] + (ab.y * K.m[5] + ab.z * K.m[8]));
+    const float f = fast_exp(-(ab.x * Mab.x + (ab.y * Mab.y + ab.z * Mab.z)));
+    const float d[3] = {-2.f * Mab.x, -2.f * Mab.y, -2.f * Mab.z}, cc[3] = {c.x, c.y, c.z};
+    float o[4] = {0.f, 0.f, 0.f, 0.f};
+    for (int i = 0; i < 3; ++i) {
+        o[0] += d[i] * f * cc[i];
+        for (int j = 0; j < 3; ++j) o[1 + j] += (d[i] * d[j] - 2.f * K.m[i * 3 + j]) * f * cc[i];
+    }
+    return F4(o[0], o[1], o[2], o[3]);
+}
 // ---------------------------------------------------------------- alternative splat kernels (GPF:1046-1082, 1142-1153, 1200-1214)
 // Modified Bessel functions K0, K1 (the reference calls boost::math::cyl_bessel_k in MaternCovariance, v = 1.5): polynomial
 // approximations of Abramowitz & Stegun 9.8.1-9.8.8, |relative error| < 3e-7, evaluated in double.
@@ -353,7 +408,7 @@ SCN_FN Levels level_ratio(const Params &P, f3 p) {
 // ---------------------------------------------------------------- cell3D / noise3D (SCN:362-395)
 // Impulse k of a cell: position draws z, y, x (g++ evaluates next3D's arguments right to left), then the sign
 // draw.  `M` is the diagonal of the kernel's inverse covariance in the units of R*p (GPF:774-802).
-SCN_FN f4 noise3d(const Params &P, f3 p, uint32_t seed, float R, f3 M) {
+SCN_FN f4 noise3d(const Params &P, f3 p, uint32_t seed, float R, const KMat &M) {
     f3 pg = xdiv3(p, R);
     f3 fl = F3(floorf(pg.x), floorf(pg.y), floorf(pg.z));
     f3 frac = xsub3(pg, fl);
@@ -414,11 +469,11 @@ struct Real { Coeff c; }; // conditioning coefficients travel with the ray (regi
 // evaluateNoise3DNormalized — world space (SCN:251-260)
 SCN_FN f4 noise3d_world(const Params &P, const Coeff &c, f3 p, uint32_t seed, float R, float kss, int add_seed, float nf, bool conditioning) {
     float ls = cov_ns_scale(P, p);
-    f3 M = se_inv_cov_diag(P, 0, 0, kss, ls);
+    KMat M = kmat_make(P, p, 0, 0, kss, ls);
     f4 n = noise3d(P, p, seed + (uint32_t)add_seed, R, M);
     n = F4(n.x / nf, n.y / nf, n.z / nf, n.w / nf);
     if (P.activate_conditioning && conditioning) {
-        f3 Mc = se_inv_cov_diag(P, 1, 0, kss, ls);
+        KMat Mc = kmat_make(P, p, 1, 0, kss, ls);
         f3 ab = F3(p.x - c.org.x, p.y - c.org.y, p.z - c.org.z);
         n = add4(n, add4(scale4(se_kernel3d(ab, Mc), c.vs), se_kernel3d_grad(ab, Mc, c.gs)));
     }
@@ -429,7 +484,7 @@ SCN_FN f4 noise3d_isoray(const Params &P, const Coeff &c, const Frame &fr, f3 p,
     f3 p_iso = cov_pos_w2l(P, p, kss);
     f3 p_ray = to_local(fr, p_iso);
     float ls = cov_ns_scale(P, p);
-    f3 M = se_inv_cov_diag(P, 0, 1, 1.0f, ls);
+    KMat M = kmat_make(P, p, 0, 1, 1.0f, ls);
     f4 nr = noise3d(P, p_ray, seed + (uint32_t)add_seed, P.R_iso, M);
     f3 g_iso = to_global(fr, F3(nr.y, nr.z, nr.w));
     f3 gw = cov_grad_l2w(P, g_iso, kss);
@@ -437,7 +492,7 @@ SCN_FN f4 noise3d_isoray(const Params &P, const Coeff &c, const Frame &fr, f3 p,
     f4 n = F4(nr.x / nf, gw.x / nf, gw.y / nf, gw.z / nf);
     if (P.activate_conditioning && conditioning) {
         f3 o_ray = to_local(fr, cov_pos_w2l(P, c.org, kss));
-        f3 Mc = se_inv_cov_diag(P, 1, 1, 1.0f, ls);
+        KMat Mc = kmat_make(P, p, 1, 1, 1.0f, ls);
         f3 ab = F3(p_ray.x - o_ray.x, p_ray.y - o_ray.y, p_ray.z - o_ray.z);
         f4 d = add4(scale4(se_kernel3d(ab, Mc), c.vs), se_kernel3d_grad(ab, Mc, c.gs));
         f3 gdw = cov_grad_l2w(P, to_global(fr, F3(d.y, d.z, d.w)), kss);
@@ -571,17 +626,15 @@ SCN_FN f3 eval_gradient(const Params &P, const Coeff &c, const Frame &fr, f3 p, 
     return F3(amp * ng.x + mg.x, amp * ng.y + mg.y, amp * ng.z + mg.z);
 }
 
-// 3x3 inverse in cofactor form (Eigen's fixed-size path), row-major
-SCN_HD void mat3_inverse(const float a[9], float r[9]) {
-#define SCN_A(i, j) a[((i) % 3) * 3 + ((j) % 3)]
-#define SCN_COF(i, j) (SCN_A(i + 1, j + 1) * SCN_A(i + 2, j + 2) - SCN_A(i + 1, j + 2) * SCN_A(i + 2, j + 1))
-    float c00 = SCN_COF(0, 0), c10 = SCN_COF(1, 0), c20 = SCN_COF(2, 0);
-    float inv = 1.0f / (c00 * a[0] + (c10 * a[3] + c20 * a[6]));
-    r[0] = c00 * inv; r[1] = c10 * inv; r[2] = c20 * inv;
-    r[3] = SCN_COF(0, 1) * inv; r[4] = SCN_COF(1, 1) * inv; r[5] = SCN_COF(2, 1) * inv;
-    r[6] = SCN_COF(0, 2) * inv; r[7] = SCN_COF(1, 2) * inv; r[8] = SCN_COF(2, 2) * inv;
-#undef SCN_COF
-#undef SCN_A
+
+// sparseConvNoiseOneOverSecondDerivative with the anisotropy field (GPF:1239-1243, 713-739): (-2 * 0.25 * invSigma^T G^-1 invSigma)^-1 v
+SCN_FN f3 one_over_second_derivative_aniso(const Params &P, f3 p_world, int is_iso, f3 v) {
+    float G[9], Gi[9], a[9], r[9]; cov_aniso3d(P, p_world, G); mat3_inverse(G, Gi);
+    float sg[3] = {1.f, 1.f, 1.f};
+    if (!is_iso) { sg[0] = P.l_aniso_inv[0]; sg[1] = P.l_aniso_inv[1]; sg[2] = P.l_aniso_inv[2]; }
+    for (int i = 0; i < 3; ++i) for (int j = 0; j < 3; ++j) a[i * 3 + j] = -2.f * (((sg[i] * Gi[i * 3 + j]) * sg[j]) * 0.25f);
+    mat3_inverse(a, r);
+    return F3(r[0] * v.x + (r[1] * v.y + r[2] * v.z), r[3] * v.x + (r[4] * v.y + r[5] * v.z), r[6] * v.x + (r[7] * v.y + r[8] * v.z));
 }
 
 // conditioning3D / conditioning1D (SCN:431-595).  The reference's residual re-evaluations only print.
@@ -606,6 +659,7 @@ SCN_FN void conditioning(const Params &P, Coeff &c, const Frame &fr, f3 p, f3 di
                 f3 gs = to_local(fr, cov_grad_w2l(P, delta, 1.0f));
                 // (-2 * 0.25 * I)^-1 = -2 I (GPF:713-739)
                 c.gs = F3(-2.f * gs.x, -2.f * gs.y, -2.f * gs.z);
+                if (P.has_aniso) c.gs = one_over_second_derivative_aniso(P, p, 1, gs);
                 if (P.multires) { float dv = L.r_lo / L.s_lo + L.r_hi / L.s_hi; c.gs = F3(c.gs.x / dv, c.gs.y / dv, c.gs.z / dv); }
                 else { float k = sqr(cov_ns_scale(P, p)); c.gs = F3(c.gs.x * k, c.gs.y * k, c.gs.z * k); }
             } else {
@@ -613,6 +667,7 @@ SCN_FN void conditioning(const Params &P, Coeff &c, const Frame &fr, f3 p, f3 di
                               -2.f * (P.l_aniso_inv[2] * P.l_aniso_inv[2] * 0.25f)};
                 float r[9]; mat3_inverse(a, r);
                 c.gs = F3(r[0] * delta.x, r[4] * delta.y, r[8] * delta.z);
+                if (P.has_aniso) c.gs = one_over_second_derivative_aniso(P, p, 0, delta);
                 if (P.multires) { float dv = L.r_lo / (L.s_lo * L.s_lo) + L.r_hi / (L.s_hi * L.s_hi); c.gs = F3(c.gs.x / dv, c.gs.y / dv, c.gs.z / dv); }
                 else { float k = sqr(cov_lateral_scale(P, p)); c.gs = F3(c.gs.x * k, c.gs.y * k, c.gs.z * k); }
             }

@@ -60,6 +60,8 @@ struct Params {
     int32_t gp_id, has_mean_add, id_add, _pad;
     scn_mean_desc mean, mean_add;
     FieldK ls, var;
+    FieldK aniso_f;            // proc_nonstationary "aniso": rotation-anisotropy field (math/GPFunctions.cpp:1678-1690); has_aniso = field present
+    int32_t has_aniso, _pad2;
     float log_base;            // logf(2.5f) from the host libm
     // alternative stationary splat kernels (math/GPFunctions.cpp:1020-1082, 1127-1214): world-space sampling only
     int32_t kernel;            // SCN_COV_SQUARED_EXPONENTIAL | SCN_COV_MATERN | SCN_COV_GABOR_ANISO | SCN_COV_GABOR_ISO

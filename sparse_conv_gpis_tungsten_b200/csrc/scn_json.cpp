@@ -205,7 +205,7 @@ int parseCov(const JVal &j, scn_medium_desc &d) {
     if (!inner) return set_error(SCN_EJSON, "proc_nonstationary: missing \"cov\"");
     if (int rc = parseSE(*inner, d, false)) return rc;
     getB(j, "multiResolutionGrid", d.multires);
-    if (j.get("aniso")) return set_error(SCN_EUNSUPPORTED, "proc_nonstationary \"aniso\" (rotation-anisotropy field) is not covered");
+    if (const JVal *v = j.get("aniso")) if (int rc = parseField(*v, d.aniso_field, false)) return rc; // math/GPFunctions.cpp:1602-1604
     if (const JVal *v = j.get("var")) if (int rc = parseField(*v, d.var, false)) return rc;
     if (const JVal *v = j.get("ls")) if (int rc = parseField(*v, d.ls, true)) return rc;
     return SCN_OK;
@@ -263,7 +263,7 @@ int desc_default(scn_medium_desc *d) {
     d->cov_type = SCN_COV_SQUARED_EXPONENTIAL;
     d->sigma = 1.f; d->length_scale = 1.f; d->aniso[0] = d->aniso[1] = d->aniso[2] = 1.f; d->kernel_scale = 3.0f;
     d->aniso_mtx[0] = d->aniso_mtx[4] = d->aniso_mtx[8] = 1.f;
-    fieldDefault(d->ls); fieldDefault(d->var);
+    fieldDefault(d->ls); fieldDefault(d->var); fieldDefault(d->aniso_field);
     d->matern_v = 1.0f; d->gabor_a_inv = 1.f; d->gabor_f_inv = 1.f; d->gabor_omega[2] = 1.f;
     return SCN_OK;
 }

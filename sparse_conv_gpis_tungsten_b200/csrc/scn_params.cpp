@@ -88,15 +88,20 @@ int params_from_desc(const scn_medium_desc &d, Params &p) {
         else if (f.type == SCN_FIELD_BOTTOM_TOP_LEFT_RIGHT) p.ls_max = (float)(std::fmax(f.max, f.min) * std::fmax(f.max2, f.min2));
         else p.ls_max = (float)std::fmax(f.max, f.min);
     }
-    field_k(d.ls, p.ls); field_k(d.var, p.var);
-    if (p.stationary) { p.ls.type = SCN_FIELD_NONE; p.var.type = SCN_FIELD_NONE; }
+    field_k(d.ls, p.ls); field_k(d.var, p.var); field_k(d.aniso_field, p.aniso_f);
+    if (p.stationary) { p.ls.type = SCN_FIELD_NONE; p.var.type = SCN_FIELD_NONE; p.aniso_f.type = SCN_FIELD_NONE; }
+    p.has_aniso = p.aniso_f.type != SCN_FIELD_NONE;
+    if (p.has_aniso && d.sampling_1d)
+        return set_error(SCN_EUNSUPPORTED, "proc_nonstationary \"aniso\" with 1D sampling reads StationaryCovariance::_local_to_world, whose off-diagonal the reference never initialises; 3D sampling only");
+    // sparseConvNoiseMaxAnisotropyScale = max(a, 1/a) with _anisotropyOnAxis = 1.5 (GPF:1741-1745, GPF.hpp:2372)
+    const float aniso_max = p.has_aniso ? 1.5f : 1.f;
     p.log_base = std::log(2.5f);
     p.world_scale = p.stationary ? 1.f : p.ls_max;
     p.add_seed_world = (int)std::floor(std::log(p.world_scale) / std::log(2.5f));
     p.R_iso = d.kernel_scale;
     {   // splattingKernelRadius(false, 1.0) (GPF:696-709, 1245-1249)
         float ls = 1.0f;
-        if (!p.stationary) { ls *= p.multires ? 1.0 : p.ls_max; ls *= 1.f; }
+        if (!p.stationary) { ls *= p.multires ? 1.0 : p.ls_max; ls *= aniso_max; }
         p.R_world = d.kernel_scale * ls * p.l_aniso_max;
     }
     p.nf_iso = std::sqrt(host_se_variance3d(p, p.R_iso, true, 1.0f, 1.0f));
@@ -107,7 +112,7 @@ int params_from_desc(const scn_medium_desc &d, Params &p) {
         float s = std::pow(2.5f, (float)k); // powf, like pow(_base, level) in SCN:64-65
         p.lvl_scale[i] = s;
         p.lvl_add_seed[i] = (int)std::floor(std::log(s) / std::log(2.5f));
-        p.lvl_R_world[i] = d.kernel_scale * s * p.l_aniso_max;
+        p.lvl_R_world[i] = d.kernel_scale * (s * aniso_max) * p.l_aniso_max;
         p.lvl_nf_world[i] = std::sqrt(host_se_variance3d(p, p.lvl_R_world[i], false, s, 1.0f));
     }
     if (alt) {

@@ -108,6 +108,14 @@ MEDIA = {
                                     covariance={"type": "matern", "sigma": 0.05, "v": 2.5, "lengthScale": 0.1, "aniso": [1, 1, 1]}),
     "gabor_aniso_world": medium(isotropic_3D_sampling=False, covariance={"type": "gabor_aniso", "sigma": 0.05, "a_inv": 0.15, "f_inv": 0.2, "omega": [1, 2, 0.5]}),
     "gabor_iso_world": medium(isotropic_3D_sampling=False, impulse_density=5, covariance={"type": "gabor_iso", "sigma": 0.05, "a_inv": 0.15, "f_inv": 0.25, "localScale": 3.5}),
+    # rotation-anisotropic non-stationary kernel (math/GPFunctions.cpp:1678-1690): full-matrix splat kernel, 3D sampling
+    "aniso_rot_world_bruteforce": medium(isotropic_3D_sampling=False, correlation_context="renewal+", single_realization=False,
+                                         covariance=_nonstat(False, aniso={"type": "noise", "noise": "left_right", "min": 0.1, "max": 0.9, "start": -1.5, "end": 1.5})),
+    "aniso_rot_iso_multires": medium(correlation_context="renewal+", single_realization=False,
+                                     covariance=_nonstat(True, aniso={"type": "noise", "noise": "bottom_top", "min": 0.2, "max": 1.2, "start": -1.0, "end": 1.0})),
+    "aniso_rot_iso_const_none": medium(covariance=_nonstat(False, aniso={"type": "constant", "val": 0.35})),
+    "aniso_rot_world_multires_renewal": medium(isotropic_3D_sampling=False, correlation_context="renewal", single_realization=False, impulse_density=4,
+                                               covariance=_nonstat(True, aniso={"type": "noise", "noise": "front_back", "min": 0.3, "max": 0.8, "start": -1.0, "end": 1.5})),
 }
 IS_1D = {k: bool(v.get("1D_sampling")) for k, v in MEDIA.items()}
 
