@@ -254,6 +254,7 @@ def run_gpu(args):
         def timed_render(sc, spp, label, sharding="interleaved"):
             wr = R.WavefrontRenderer(sc, device=local, rank=rank, world=world, sharding=sharding); wr.render(1); R.gather_image_rgb(wr, world); wr.close()  # warm-up (kernels, NCCL all_gather connections)
             wr = R.WavefrontRenderer(sc, device=local, rank=rank, world=world, sharding=sharding)
+            wr.prepare(spp)  # wavefront buffers allocated outside the timed region
             torch.cuda.synchronize()
             if world > 1:
                 dist.barrier()

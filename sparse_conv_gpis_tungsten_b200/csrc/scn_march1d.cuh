@@ -97,11 +97,15 @@ __global__ void __launch_bounds__(MARCH1D_BLOCK) k_march1d(const __grid_constant
     uint32_t seed = 0, evals = 0; float near_t = 0.f, oz = 0.f, cvs = 0.f, cgz = 0.f;
     double t = 0, pf = 0, dstep = 0, dfar = 0, intp = 0, ta = 0, t_prev = 0, t_test = 0;
     int sign0 = 1, gp_id = 0; bool first_step = false, first_scatter = true, conditioned = false;
-    // register cache: impulses of cells ci - 1, ci, ci + 1
-    int ci = 0; bool cvalid = false;
-    float im[NIMP], i0[NIMP], ip[NIMP]; uint32_t sm = 0u, s0 = 0u, sp = 0u;
+    // register cache: a window of FOUR consecutive cells cb .. cb + 3 (an evaluation in cell i reads i - 1, i, i + 1, so the window serves
+    // i = cb + 1 and i = cb + 2).  The spare cell is what lets the regeneration run converged: a lane MUST move its window when it enters
+    // cb + 3, and whenever any lane of the warp must, every lane already in cb + 2 moves too (one cell early).  After such a round every
+    // lane is at least one full cell away from its next forced move, so rounds happen about once per cell length (~21 steps) with most
+    // lanes taking part, instead of each lane regenerating on its own iteration with one or two lanes active.
+    int cb = 0; bool cvalid = false;
+    float w0[NIMP], w1[NIMP], w2[NIMP], w3[NIMP]; uint32_t wsig = 0u; // sign bits: 4 per slot
 #pragma unroll
-    for (int k = 0; k < NIMP; ++k) { im[k] = 0.f; i0[k] = 0.f; ip[k] = 0.f; }
+    for (int k = 0; k < NIMP; ++k) { w0[k] = 0.f; w1[k] = 0.f; w2[k] = 0.f; w3[k] = 0.f; }
 
     for (;;) {
         // ------------------------------------------------------------ fetch rays for idle lanes (warp-aggregated atomic)
@@ -166,31 +170,50 @@ __global__ void __launch_bounds__(MARCH1D_BLOCK) k_march1d(const __grid_constant
 
         // ------------------------------------------------------------ evaluateValue (SCN:73-89) through the register cache
         float fval = 0.f; int id = 0;
+        f3 p = F3(0.f, 0.f, 0.f); float z = 0.f, frac = 0.f; int i = 0, nshift = 0; bool must = false;
         if (active) {
             const double te = phase == PH_F0 ? (double)near_t : (phase == PH_MARCH ? t : (phase == PH_REFINE ? t_test : dfar));
-            const f3 p = ray_at(o, rd, te);
+            p = ray_at(o, rd, te);
             // transformPosDirWorldtoLocal (GPF:631-633; the division by localScale = 1 is exact), z of the ray frame
-            const float z = xdot(frn, xmul3(l_inv(P), p));
-            const float tg = xdiv(z, R), fl = floorf(tg), frac = xsub(tg, fl);
-            const int i = (int)fl;
-            if (!cvalid || i != ci) {
-                if (cvalid && i == ci + 1) { // the common case: one cell forward
+            z = xdot(frn, xmul3(l_inv(P), p));
+            const float tg = xdiv(z, R), fl = floorf(tg);
+            frac = xsub(tg, fl); i = (int)fl;
+            if (!cvalid || i < cb + 1 || i > cb + 3) nshift = 4; // new ray / jump: build cells i - 1 .. i + 2
+            else if (i == cb + 3) { nshift = 1; must = true; }
+            else if (i == cb + 2) nshift = 1; // one cell early, taken only when some lane of the warp must move
+        }
+        // a lane that starts a ray (or jumped): lanes 0..3 generate its four cells side by side and hand them over by shuffles
+        unsigned ms = __ballot_sync(FULL, nshift == 4);
+        while (ms) {
+            const int T = __ffs(ms) - 1; ms &= ms - 1;
+            const int ti = __shfl_sync(FULL, i, T); const uint32_t ts = __shfl_sync(FULL, seed, T);
+            float g[NIMP]; uint32_t plus = 0u;
 #pragma unroll
-                    for (int k = 0; k < NIMP; ++k) { im[k] = i0[k]; i0[k] = ip[k]; }
-                    sm = s0; s0 = sp;
-                    cell1d_generate<NIMP>((uint32_t)(i + 1), seed, ip, sp);
-                } else if (cvalid && i == ci - 1) { // secant refinement stepping back over a cell boundary
+            for (int k = 0; k < NIMP; ++k) g[k] = 0.f;
+            if (lane < 4) cell1d_generate<NIMP>((uint32_t)(ti - 1 + lane), ts, g, plus);
 #pragma unroll
-                    for (int k = 0; k < NIMP; ++k) { ip[k] = i0[k]; i0[k] = im[k]; }
-                    sp = s0; s0 = sm;
-                    cell1d_generate<NIMP>((uint32_t)(i - 1), seed, im, sm);
-                } else {
-                    cell1d_generate<NIMP>((uint32_t)(i - 1), seed, im, sm);
-                    cell1d_generate<NIMP>((uint32_t)i, seed, i0, s0);
-                    cell1d_generate<NIMP>((uint32_t)(i + 1), seed, ip, sp);
-                }
-                ci = i; cvalid = true;
+            for (int k = 0; k < NIMP; ++k) {
+                const float a0 = __shfl_sync(FULL, g[k], 0), a1 = __shfl_sync(FULL, g[k], 1), a2 = __shfl_sync(FULL, g[k], 2), a3 = __shfl_sync(FULL, g[k], 3);
+                if (lane == T) { w0[k] = a0; w1[k] = a1; w2[k] = a2; w3[k] = a3; }
             }
+            const uint32_t pw = __shfl_sync(FULL, plus, 0) | (__shfl_sync(FULL, plus, 1) << 4) | (__shfl_sync(FULL, plus, 2) << 8) | (__shfl_sync(FULL, plus, 3) << 12);
+            if (lane == T) { wsig = pw; cb = ti - 1; cvalid = true; }
+        }
+        if (__any_sync(FULL, must)) { // a round: every lane in the upper half of its window moves one cell forward
+            if (nshift == 1) {
+#pragma unroll
+                for (int k = 0; k < NIMP; ++k) { w0[k] = w1[k]; w1[k] = w2[k]; w2[k] = w3[k]; }
+                cb += 1;
+                uint32_t plus; cell1d_generate<NIMP>((uint32_t)(cb + 3), seed, w3, plus);
+                wsig = (wsig >> 4) | (plus << 12);
+            }
+        }
+        if (active) {
+            const bool hi = i == cb + 2; // which three of the four cached cells are i - 1, i, i + 1
+            float im[NIMP], i0[NIMP], ip[NIMP];
+#pragma unroll
+            for (int k = 0; k < NIMP; ++k) { im[k] = hi ? w1[k] : w0[k]; i0[k] = hi ? w2[k] : w1[k]; ip[k] = hi ? w3[k] : w2[k]; }
+            const uint32_t sg = hi ? wsig >> 4 : wsig, sm = sg & 15u, s0 = (sg >> 4) & 15u, sp = (sg >> 8) & 15u;
             // noise1D (SCN:397-406): cells dx = -1, 0, +1 in this order, per-cell partial sums
             float sv = 0.f;
 #pragma unroll

@@ -231,6 +231,11 @@ class WavefrontRenderer:
         self.paths = p
         self._buf_n = n
 
+    def prepare(self, spp):
+        """Allocate the wavefront buffers a render(spp) call will use (so that a timed render does not include cudaMalloc)."""
+        if self.n_pixels:
+            self._alloc(self.n_pixels * max(1, min(spp, self.max_paths // self.n_pixels)))
+
     def render(self, spp, count_queries=False):
         """Add `spp` samples per pixel to this rank's framebuffer slice.  Samples are processed in chunks so that a wavefront
         holds at most max_paths paths."""
