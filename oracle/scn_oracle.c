@@ -130,6 +130,10 @@ static frame_t frame_make(v3 nin) {
 static inline v3 frame_to_local(const frame_t *f, v3 p) { return V3(v3_dot(f->t, p), v3_dot(f->b, p), v3_dot(f->n, p)); }
 static inline v3 frame_to_global(const frame_t *f, v3 p) { return v3_add(v3_add(v3_scale(f->t, p.x), v3_scale(f->b, p.y)), v3_scale(f->n, p.z)); }
 
+static void mat3_inverse(const float a[9], float r[9]); /* Eigen's fixed-size 3x3 inverse (cofactor form), defined below */
+/* Eigen's fixed-size products reduce three terms as x0 + (x1 + x2) */
+static inline v3 mat3_mulv_e(const float a[9], v3 b) { return V3(a[0] * b.x + (a[1] * b.y + a[2] * b.z), a[3] * b.x + (a[4] * b.y + a[5] * b.z), a[6] * b.x + (a[7] * b.y + a[8] * b.z)); }
+static inline v3 mat3_tmulv_e(const float a[9], v3 b) { return V3(a[0] * b.x + (a[3] * b.y + a[6] * b.z), a[1] * b.x + (a[4] * b.y + a[7] * b.z), a[2] * b.x + (a[5] * b.y + a[8] * b.z)); }
 /* ------------------------------------------------------------------ medium */
 struct orc_medium {
     scn_medium_desc d;
@@ -141,12 +145,13 @@ struct orc_medium {
     int absorption_only;
     int kernel;              /* SCN_COV_SQUARED_EXPONENTIAL | SCN_COV_MATERN | SCN_COV_GABOR_ANISO | SCN_COV_GABOR_ISO */
     float k_a, k_f; v3 k_omega; /* Gabor: _a, _f, _omega (GPF:1087-1097) */
+    int use_mtx;             /* "useAnisoMtx": full matrices (GPF:668-675), row-major: L = _local_to_world, W = _world_to_local, C = _cov_mtx_inv */
+    float L[9], W[9], C[9], C_det;
     int has_aniso;           /* proc_nonstationary "aniso" field: rotation anisotropy of the splat kernel (GPF:1678-1690) */
 };
 
 orc_medium *orc_medium_create(const scn_medium_desc *desc) {
     if (!desc) { snprintf(g_err, sizeof g_err, "null desc"); return NULL; }
-    if (desc->use_aniso_mtx) { snprintf(g_err, sizeof g_err, "useAnisoMtx is not covered"); return NULL; }
     orc_medium *m = (orc_medium *)calloc(1, sizeof *m);
     m->d = *desc;
     m->n_imp = (uint32_t)desc->impulse_density;
@@ -168,6 +173,15 @@ orc_medium *orc_medium_create(const scn_medium_desc *desc) {
     if (isinf(m->l_aniso_inv.x) || isnan(m->l_aniso_inv.x)) m->l_aniso_inv.x = 0;
     if (isinf(m->l_aniso_inv.y) || isnan(m->l_aniso_inv.y)) m->l_aniso_inv.y = 0;
     if (isinf(m->l_aniso_inv.z) || isnan(m->l_aniso_inv.z)) m->l_aniso_inv.z = 0;
+    m->use_mtx = desc->use_aniso_mtx != 0;
+    if (m->use_mtx) { /* GPF:668-675 */
+        if (m->kernel != SCN_COV_SQUARED_EXPONENTIAL || m->has_aniso) { snprintf(g_err, sizeof g_err, "useAnisoMtx: squared-exponential kernel without an anisotropy field only"); free(m); return NULL; }
+        for (int i = 0; i < 9; ++i) m->L[i] = m->l_conv * desc->aniso_mtx[i];
+        mat3_inverse(m->L, m->W);
+        for (int i = 0; i < 3; ++i) for (int j = 0; j < 3; ++j) m->C[i * 3 + j] = m->W[0 * 3 + i] * m->W[0 * 3 + j] + (m->W[1 * 3 + i] * m->W[1 * 3 + j] + m->W[2 * 3 + i] * m->W[2 * 3 + j]);
+        const float *c = m->C; /* Eigen's 3x3 determinant (LU/Determinant.h: bruteforce_det3_helper) */
+        m->C_det = c[0] * (c[4] * c[8] - c[5] * c[7]) - c[1] * (c[3] * c[8] - c[5] * c[6]) + c[2] * (c[3] * c[7] - c[4] * c[6]);
+    }
     m->ls_max = 1.f;
     if (!m->stationary && desc->ls.type != SCN_FIELD_NONE) {
         const scn_field_desc *f = &desc->ls;
@@ -246,6 +260,7 @@ static float cov_radius(const orc_medium *m, int is_identity, float local_scale)
     if (m->kernel == SCN_COV_GABOR_ISO) return (float)(sf * sqrt(2) / 4 * 1.0 / m->k_a);   /* GPF:1185-1188 */
     if (is_identity) return sf;
     float mf = max3f(m->l_aniso.x, m->l_aniso.y, m->l_aniso.z);
+    if (m->use_mtx) mf = max3f((m->L[0] + m->L[1]) + m->L[2], (m->L[3] + m->L[4]) + m->L[5], (m->L[6] + m->L[7]) + m->L[8]); /* col0 + col1 + col2, GPF:704-706 */
     return sf * local_scale * mf;
 }
 /* Matern / Gabor sparseConvNoiseVariance3D (GPF:1029-1044, 1134-1138, 1192-1196) */
@@ -302,7 +317,11 @@ static v4 alt_kernel3d(const orc_medium *m, v3 ab) {
 static float se_variance3d(const orc_medium *m, float density, float R, int is_identity, float global_scale, float local_scale) {
     double per_unit = density / (R * R * R);
     double det_sqrt = 1.0;
-    if (!is_identity) { det_sqrt = m->l_aniso.x * m->l_aniso.y * m->l_aniso.z; det_sqrt *= pow(global_scale, 3); }
+    if (!is_identity) {
+        det_sqrt = m->l_aniso.x * m->l_aniso.y * m->l_aniso.z;
+        if (m->use_mtx) det_sqrt = 1.0 / sqrt(m->C_det); /* GPF:748-749 */
+        det_sqrt *= pow(global_scale, 3);
+    }
     det_sqrt *= pow(local_scale, 3);
     double integral = pow(M_PI, 1.5) * det_sqrt;
     return (float)(per_unit * integral);
@@ -322,9 +341,9 @@ static float cov_variance1d(const orc_medium *m, v3 p, float density, float R) {
 }
 /* transforms (GPF:631-637, 1261-1284): diagonal world<->iso matrices */
 static inline float tr_scale(const orc_medium *m, float s) { return m->stationary ? s : (m->multires ? s : m->ls_max); }
-static v3 cov_pos_w2l(const orc_medium *m, v3 v, float s) { s = tr_scale(m, s); return v3_div(v3_mul(m->l_aniso_inv, v), s); }
-static v3 cov_grad_w2l(const orc_medium *m, v3 v, float s) { s = tr_scale(m, s); return v3_scale(v3_mul(m->l_aniso, v), s); }
-static v3 cov_grad_l2w(const orc_medium *m, v3 v, float s) { s = tr_scale(m, s); return v3_div(v3_mul(m->l_aniso_inv, v), s); }
+static v3 cov_pos_w2l(const orc_medium *m, v3 v, float s) { s = tr_scale(m, s); return v3_div(m->use_mtx ? mat3_mulv_e(m->W, v) : v3_mul(m->l_aniso_inv, v), s); }
+static v3 cov_grad_w2l(const orc_medium *m, v3 v, float s) { s = tr_scale(m, s); return v3_scale(m->use_mtx ? mat3_tmulv_e(m->L, v) : v3_mul(m->l_aniso, v), s); }
+static v3 cov_grad_l2w(const orc_medium *m, v3 v, float s) { s = tr_scale(m, s); return v3_div(m->use_mtx ? mat3_tmulv_e(m->W, v) : v3_mul(m->l_aniso_inv, v), s); }
 /* getNonstationaryCovSplatCov1D (GPF.hpp:1213, GPF:1716-1727, no anisotropy field) */
 static float cov_splat_cov1d(const orc_medium *m, v3 pq, v3 pc) {
     if (m->stationary) return 1.0f;
@@ -355,6 +374,10 @@ static void se_inv_cov_full(const orc_medium *m, const float aniso_inv[9], int i
     for (int i = 0; i < 9; ++i) { if (is_cov) M[i] *= 0.5f; M[i] /= sqrf(ls); M[i] *= 0.5f; }
 }
 
+/* getInvCovMtx with "useAnisoMtx", not isotropic (GPF:791-801): _cov_mtx_inv / gs^2, then the isCov / localScale / 0.5 factors */
+static void se_inv_cov_mtx(const orc_medium *m, int is_cov, float gs, float ls, float M[9]) {
+    for (int i = 0; i < 9; ++i) { M[i] = m->C[i] / sqrf(gs); if (is_cov) M[i] *= 0.5f; M[i] /= sqrf(ls); M[i] *= 0.5f; }
+}
 /* getInvCovMtx diagonal (GPF:774-802) */
 static v3 se_inv_cov_diag(const orc_medium *m, int is_cov, int is_iso, float gs, float ls) {
     v3 d = V3(1.f, 1.f, 1.f);
@@ -373,8 +396,10 @@ static v4 cov_kernel3d(const orc_medium *m, v3 pa, v3 pb, int is_cov, int is_iso
     v3 ab = v3_sub(pa, pb);
     if (m->kernel != SCN_COV_SQUARED_EXPONENTIAL) return alt_kernel3d(m, ab);
     float G[9];
-    if (cov_aniso3d(m, p_world, G)) { /* GPF:556-558: aniso_inv = inverse, full matrix */
-        float Gi[9], Mf[9]; mat3_inverse(G, Gi); se_inv_cov_full(m, Gi, is_cov, is_iso, gs, ls, Mf);
+    int full = cov_aniso3d(m, p_world, G);
+    if (full || (m->use_mtx && !is_iso)) { /* GPF:556-558: aniso_inv = inverse, full matrix; GPF:791-795: _cov_mtx_inv / gs^2 */
+        float Gi[9], Mf[9];
+        if (full) { mat3_inverse(G, Gi); se_inv_cov_full(m, Gi, is_cov, is_iso, gs, ls, Mf); } else se_inv_cov_mtx(m, is_cov, gs, ls, Mf);
         /* dist2_ab = (ab^T M) ab and ab . M.col(j) (GPF.hpp:76-78, GPF:804-817), three-term sums as x0 + (x1 + x2) */
         v3 Mab = V3(ab.x * Mf[0] + (ab.y * Mf[3] + ab.z * Mf[6]), ab.x * Mf[1] + (ab.y * Mf[4] + ab.z * Mf[7]), ab.x * Mf[2] + (ab.y * Mf[5] + ab.z * Mf[8]));
         float f = expf(-(Mab.x * ab.x + (Mab.y * ab.y + Mab.z * ab.z)));
@@ -390,8 +415,10 @@ static v4 cov_kernel3d_grad(const orc_medium *m, v3 pa, v3 pb, v3 c, int is_cov,
     float ls = cov_ns_scale(m, p_world);
     v3 ab = v3_sub(pa, pb);
     float G[9];
-    if (cov_aniso3d(m, p_world, G)) { /* GPF:565-577, 819-833 with the full matrix */
-        float Gi[9], Mf[9]; mat3_inverse(G, Gi); se_inv_cov_full(m, Gi, is_cov, is_iso, gs, ls, Mf);
+    int full = cov_aniso3d(m, p_world, G);
+    if (full || (m->use_mtx && !is_iso)) { /* GPF:565-577, 819-833 with the full matrix */
+        float Gi[9], Mf[9];
+        if (full) { mat3_inverse(G, Gi); se_inv_cov_full(m, Gi, is_cov, is_iso, gs, ls, Mf); } else se_inv_cov_mtx(m, is_cov, gs, ls, Mf);
         /* dist2_ab = (ab^T M) ab and ab . M.col(j) (GPF.hpp:76-78, GPF:804-817), three-term sums as x0 + (x1 + x2) */
         v3 Mab = V3(ab.x * Mf[0] + (ab.y * Mf[3] + ab.z * Mf[6]), ab.x * Mf[1] + (ab.y * Mf[4] + ab.z * Mf[7]), ab.x * Mf[2] + (ab.y * Mf[5] + ab.z * Mf[8]));
         float f = expf(-(Mab.x * ab.x + (Mab.y * ab.y + Mab.z * ab.z)));
@@ -756,6 +783,12 @@ static v3 cov_one_over_second_derivative_diag(const orc_medium *m, int is_iso) {
 /* sparseConvNoiseOneOverSecondDerivative with the anisotropy field (GPF:1239-1243, 713-739): (-2 * 0.25 * invSigma^T G^-1 invSigma)^-1 applied to v */
 static v3 cov_one_over_second_derivative_apply(const orc_medium *m, v3 p_world, int is_iso, v3 v) {
     float G[9];
+    if (m->use_mtx && !is_iso) { /* GPF:728-738 with _cov_mtx_inv */
+        float a[9], r[9];
+        for (int i = 0; i < 9; ++i) a[i] = -2.f * (m->C[i] * 0.25f);
+        mat3_inverse(a, r);
+        return mat3_mulv_e(r, v);
+    }
     if (!cov_aniso3d(m, p_world, G)) return v3_mul(cov_one_over_second_derivative_diag(m, is_iso), v);
     float Gi[9], a[9], r[9]; mat3_inverse(G, Gi);
     float sg[3] = {1.f, 1.f, 1.f};
@@ -855,6 +888,11 @@ static void real_nee_shared(const real_t *r, v3 dir, v3 normal, v3 p, const info
     v3 w = m->stationary ? m->l_aniso_inv : v3_div(m->l_aniso_inv, sc);
     float wd[3] = {amp * w.x, amp * w.y, amp * w.z};
     for (int i = 0; i < 3; ++i) for (int j = 0; j < 3; ++j) o->mtx[3 * i + j] = wd[i] * rc[3 * i + j];
+    if (m->use_mtx) { /* amplitude * _world_to_local_transpose (/ scale) * mtx_ray_coord (SCN:618, GPF:649, 1281-1284) */
+        float wt[9];
+        for (int i = 0; i < 3; ++i) for (int j = 0; j < 3; ++j) wt[i * 3 + j] = amp * (m->stationary ? m->W[j * 3 + i] : m->W[j * 3 + i] / sc);
+        for (int i = 0; i < 3; ++i) for (int j = 0; j < 3; ++j) o->mtx[3 * i + j] = wt[i * 3 + 0] * rc[0 * 3 + j] + (wt[i * 3 + 1] * rc[1 * 3 + j] + wt[i * 3 + 2] * rc[2 * 3 + j]);
+    }
     float inv[9]; mat3_inverse(o->mtx, inv);
     float R = cov_radius(m, 1, 1.0f);
     if (!m->multires) { v4 n = real_noise1d_norm(r, p, dir, seed, R, 1.0f, 1, 0); o->gcon = V3(n.y, n.z, n.w); }

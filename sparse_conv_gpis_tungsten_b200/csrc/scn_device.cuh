@@ -164,9 +164,18 @@ SCN_HD float cov_amplitude(const Params &P, f3 p) { // sparseConvNoiseAmplitude
 SCN_HD float tr_scale(const Params &P, float s) { return P.stationary ? s : (P.multires ? s : P.ls_max); }
 SCN_HD f3 l_inv(const Params &P) { return F3(P.l_aniso_inv[0], P.l_aniso_inv[1], P.l_aniso_inv[2]); }
 SCN_HD f3 l_fwd(const Params &P) { return F3(P.l_aniso[0], P.l_aniso[1], P.l_aniso[2]); }
-SCN_HD f3 cov_pos_w2l(const Params &P, f3 v, float s) { return xdiv3(xmul3(l_inv(P), v), tr_scale(P, s)); }   // GPF:631-633
-SCN_HD f3 cov_grad_w2l(const Params &P, f3 v, float s) { return xscale3(xmul3(l_fwd(P), v), tr_scale(P, s)); } // GPF:639
-SCN_HD f3 cov_grad_l2w(const Params &P, f3 v, float s) { return xdiv3(xmul3(l_inv(P), v), tr_scale(P, s)); }  // GPF:641
+// "useAnisoMtx": full 3x3 transforms (GPF:668-675); Eigen's fixed-size products reduce three terms as x0 + (x1 + x2), separately rounded
+SCN_HD f3 mtx_mulv(const float a[9], f3 b) {
+    return F3(xadd(xmul(a[0], b.x), xadd(xmul(a[1], b.y), xmul(a[2], b.z))), xadd(xmul(a[3], b.x), xadd(xmul(a[4], b.y), xmul(a[5], b.z))),
+              xadd(xmul(a[6], b.x), xadd(xmul(a[7], b.y), xmul(a[8], b.z))));
+}
+SCN_HD f3 mtx_tmulv(const float a[9], f3 b) {
+    return F3(xadd(xmul(a[0], b.x), xadd(xmul(a[3], b.y), xmul(a[6], b.z))), xadd(xmul(a[1], b.x), xadd(xmul(a[4], b.y), xmul(a[7], b.z))),
+              xadd(xmul(a[2], b.x), xadd(xmul(a[5], b.y), xmul(a[8], b.z))));
+}
+SCN_HD f3 cov_pos_w2l(const Params &P, f3 v, float s) { return xdiv3(P.use_mtx ? mtx_mulv(P.mW, v) : xmul3(l_inv(P), v), tr_scale(P, s)); }     // GPF:631-633
+SCN_HD f3 cov_grad_w2l(const Params &P, f3 v, float s) { return xscale3(P.use_mtx ? mtx_tmulv(P.mL, v) : xmul3(l_fwd(P), v), tr_scale(P, s)); } // GPF:639
+SCN_HD f3 cov_grad_l2w(const Params &P, f3 v, float s) { return xdiv3(P.use_mtx ? mtx_tmulv(P.mW, v) : xmul3(l_inv(P), v), tr_scale(P, s)); }    // GPF:641
 SCN_HD float cov_splat_cov1d(const Params &P, f3 pq, f3 pc) { // getNonstationaryCovSplatCov1D
     if (P.stationary) return 1.0f;
     float s = (float)(0.5 * (double)(sqr(cov_ns_scale(P, pq)) + sqr(cov_ns_scale(P, pc))));
@@ -176,7 +185,7 @@ SCN_HD float cov_splat_cov1d(const Params &P, f3 pq, f3 pc) { // getNonstationar
 SCN_HD float se_variance3d(const Params &P, float R, int is_identity, float gs, float ls) {
     double per_unit = (double)xdiv(P.density, xmul(xmul(R, R), R));
     double det_sqrt = 1.0;
-    if (!is_identity) { det_sqrt = (double)xmul(xmul(P.l_aniso[0], P.l_aniso[1]), P.l_aniso[2]); det_sqrt *= (double)gs * (double)gs * (double)gs; }
+    if (!is_identity) { det_sqrt = P.use_mtx ? P.mC_dsi : (double)xmul(xmul(P.l_aniso[0], P.l_aniso[1]), P.l_aniso[2]); det_sqrt *= (double)gs * (double)gs * (double)gs; }
     det_sqrt *= (double)ls * (double)ls * (double)ls;
     return (float)(per_unit * (5.568327996831707 * det_sqrt)); // pow(M_PI, 1.5)
 }
@@ -236,8 +245,13 @@ SCN_FN void cov_aniso3d(const Params &P, f3 p_world, float G[9]) {
 // invSigma^T G^-1 invSigma with the isCov / localScale / 0.5 factors of getInvCovMtx (GPF:774-802)
 struct KMat { bool full; f3 d; float m[9]; };
 SCN_FN KMat kmat_make(const Params &P, f3 p_world, int is_cov, int is_iso, float gs, float ls) {
-    KMat K; K.full = P.has_aniso != 0; K.d = F3(0.f, 0.f, 0.f);
+    KMat K; K.full = P.has_aniso != 0 || (P.use_mtx && !is_iso); K.d = F3(0.f, 0.f, 0.f);
     if (!K.full) { K.d = se_inv_cov_diag(P, is_cov, is_iso, gs, ls); return K; }
+    if (!P.has_aniso) { // "useAnisoMtx" (GPF:791-801): _cov_mtx_inv / gs^2, then the isCov / localScale / 0.5 factors
+        const float k = (is_cov ? 0.5f : 1.0f), l2 = ls * ls, g2 = gs * gs;
+        for (int i = 0; i < 9; ++i) K.m[i] = P.mC[i] / g2 * k / l2 * 0.5f;
+        return K;
+    }
     float G[9], Gi[9]; cov_aniso3d(P, p_world, G); mat3_inverse(G, Gi);
     float sg[3] = {1.f, 1.f, 1.f};
     if (!is_iso) { sg[0] = P.l_aniso_inv[0] / gs; sg[1] = P.l_aniso_inv[1] / gs; sg[2] = P.l_aniso_inv[2] / gs; }
@@ -668,6 +682,12 @@ SCN_FN void conditioning(const Params &P, Coeff &c, const Frame &fr, f3 p, f3 di
                 float r[9]; mat3_inverse(a, r);
                 c.gs = F3(r[0] * delta.x, r[4] * delta.y, r[8] * delta.z);
                 if (P.has_aniso) c.gs = one_over_second_derivative_aniso(P, p, 0, delta);
+                else if (P.use_mtx) { // GPF:728-738 with _cov_mtx_inv
+                    float am[9], rm[9];
+                    for (int i = 0; i < 9; ++i) am[i] = -2.f * (P.mC[i] * 0.25f);
+                    mat3_inverse(am, rm);
+                    c.gs = F3(rm[0] * delta.x + (rm[1] * delta.y + rm[2] * delta.z), rm[3] * delta.x + (rm[4] * delta.y + rm[5] * delta.z), rm[6] * delta.x + (rm[7] * delta.y + rm[8] * delta.z));
+                }
                 if (P.multires) { float dv = L.r_lo / (L.s_lo * L.s_lo) + L.r_hi / (L.s_hi * L.s_hi); c.gs = F3(c.gs.x / dv, c.gs.y / dv, c.gs.z / dv); }
                 else { float k = sqr(cov_lateral_scale(P, p)); c.gs = F3(c.gs.x * k, c.gs.y * k, c.gs.z * k); }
             }
@@ -706,6 +726,12 @@ SCN_FN void nee_shared(const Params &P, const Coeff &c, f3 dir, f3 normal, f3 p,
     float wd[3] = {amp * (P.stationary ? P.l_aniso_inv[0] : P.l_aniso_inv[0] / sc), amp * (P.stationary ? P.l_aniso_inv[1] : P.l_aniso_inv[1] / sc),
                    amp * (P.stationary ? P.l_aniso_inv[2] : P.l_aniso_inv[2] / sc)};
     float m[9] = {wd[0] * fr.t.x, wd[0] * fr.b.x, wd[0] * fr.n.x, wd[1] * fr.t.y, wd[1] * fr.b.y, wd[1] * fr.n.y, wd[2] * fr.t.z, wd[2] * fr.b.z, wd[2] * fr.n.z};
+    if (P.use_mtx) { // amplitude * _world_to_local_transpose (/ scale) * mtx_ray_coord (SCN:618, GPF:649, 1281-1284)
+        const float rc[9] = {fr.t.x, fr.b.x, fr.n.x, fr.t.y, fr.b.y, fr.n.y, fr.t.z, fr.b.z, fr.n.z};
+        float wt[9];
+        for (int i = 0; i < 3; ++i) for (int j = 0; j < 3; ++j) wt[i * 3 + j] = amp * (P.stationary ? P.mW[j * 3 + i] : P.mW[j * 3 + i] / sc);
+        for (int i = 0; i < 3; ++i) for (int j = 0; j < 3; ++j) m[3 * i + j] = wt[i * 3] * rc[j] + (wt[i * 3 + 1] * rc[3 + j] + wt[i * 3 + 2] * rc[6 + j]);
+    }
     float inv[9]; mat3_inverse(m, inv);
     if (!P.multires) { f4 n = noise1d_norm(P, c, fr, p, seed, 1.0f, 0, true, false); o.gcon = F3(n.y, n.z, n.w); }
     else {

@@ -21,7 +21,7 @@
 
 namespace scn {
 
-inline bool fast_noise3d_supported(const Params &P) { return P.stationary && P.kernel == SCN_COV_SQUARED_EXPONENTIAL && !P.sampling_1d && P.n_imp > 0; }
+inline bool fast_noise3d_supported(const Params &P) { return P.stationary && !P.use_mtx && P.kernel == SCN_COV_SQUARED_EXPONENTIAL && !P.sampling_1d && P.n_imp > 0; }
 
 constexpr int FAST_BLOCK = 128;
 

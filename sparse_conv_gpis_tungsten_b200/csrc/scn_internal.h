@@ -61,7 +61,11 @@ struct Params {
     scn_mean_desc mean, mean_add;
     FieldK ls, var;
     FieldK aniso_f;            // proc_nonstationary "aniso": rotation-anisotropy field (math/GPFunctions.cpp:1678-1690); has_aniso = field present
-    int32_t has_aniso, _pad2;
+    int32_t has_aniso;
+    // "useAnisoMtx" (math/GPFunctions.cpp:668-675), row-major: mL = _local_to_world = l_conv * anisoMtx, mW = its inverse, mC = mW^T mW
+    int32_t use_mtx;
+    float mL[9], mW[9], mC[9], _pad3;
+    double mC_dsi;             // 1 / sqrt(det mC) (GPF:749), host libm
     float log_base;            // logf(2.5f) from the host libm
     // alternative stationary splat kernels (math/GPFunctions.cpp:1020-1082, 1127-1214): world-space sampling only
     int32_t kernel;            // SCN_COV_SQUARED_EXPONENTIAL | SCN_COV_MATERN | SCN_COV_GABOR_ANISO | SCN_COV_GABOR_ISO

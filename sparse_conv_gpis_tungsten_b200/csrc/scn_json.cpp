@@ -192,7 +192,13 @@ int parseSE(const JVal &j, scn_medium_desc &d, bool allowAlt) {
     }
     getF(j, "sigma", d.sigma); getF(j, "lengthScale", d.length_scale); getVec3(j, "aniso", d.aniso);
     getB(j, "useAnisoMtx", d.use_aniso_mtx);
-    if (d.use_aniso_mtx) return set_error(SCN_EUNSUPPORTED, "\"useAnisoMtx\" (full anisotropy matrix) is not covered");
+    if (d.use_aniso_mtx) { // "anisoMtx": nine numbers, row-major (io/JsonPtr.cpp:188-198, math/GPFunctions.cpp:669)
+        const JVal *v = j.get("anisoMtx");
+        if (v) {
+            if (v->kind != JVal::Arr || v->arr.size() != 9) return set_error(SCN_EJSON, "anisoMtx: expecting an array of 9 numbers");
+            for (int i = 0; i < 9; ++i) { if (v->arr[i].kind != JVal::Num) return set_error(SCN_EJSON, "anisoMtx: expecting numbers"); d.aniso_mtx[i] = (float)v->arr[i].num; }
+        }
+    }
     return SCN_OK;
 }
 

@@ -28,7 +28,7 @@
 namespace scn {
 
 inline bool march1d_supported(const Params &P) {
-    return P.sampling_1d && P.stationary && !P.multires && P.kernel == SCN_COV_SQUARED_EXPONENTIAL && P.n_imp >= 1 && P.n_imp <= 4;
+    return P.sampling_1d && P.stationary && !P.multires && !P.use_mtx && P.kernel == SCN_COV_SQUARED_EXPONENTIAL && P.n_imp >= 1 && P.n_imp <= 4;
 }
 
 #if defined(__CUDACC__)

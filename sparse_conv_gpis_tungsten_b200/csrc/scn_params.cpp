@@ -23,10 +23,20 @@ const char *last_error() { return g_err; }
 static float host_se_variance3d(const Params &p, float R, bool is_identity, float gs, float ls) { // GPF:741-754
     double per_unit = p.density / (R * R * R);
     double det_sqrt = 1.0;
-    if (!is_identity) { det_sqrt = p.l_aniso[0] * p.l_aniso[1] * p.l_aniso[2]; det_sqrt *= std::pow((double)gs, 3); }
+    if (!is_identity) { det_sqrt = p.l_aniso[0] * p.l_aniso[1] * p.l_aniso[2]; if (p.use_mtx) det_sqrt = p.mC_dsi; det_sqrt *= std::pow((double)gs, 3); }
     det_sqrt *= std::pow((double)ls, 3);
     double integral = std::pow(M_PI, 1.5) * det_sqrt;
     return (float)(per_unit * integral);
+}
+// Eigen's fixed-size 3x3 inverse (cofactor form, LU/InverseImpl.h:141-179), row-major
+static void host_mat3_inverse(const float a[9], float r[9]) {
+    auto A = [&](int i, int j) { return a[(i % 3) * 3 + (j % 3)]; };
+    auto cof = [&](int i, int j) { return A(i + 1, j + 1) * A(i + 2, j + 2) - A(i + 1, j + 2) * A(i + 2, j + 1); };
+    float c00 = cof(0, 0), c10 = cof(1, 0), c20 = cof(2, 0);
+    float inv = 1.0f / (c00 * a[0] + (c10 * a[3] + c20 * a[6]));
+    r[0] = c00 * inv; r[1] = c10 * inv; r[2] = c20 * inv;
+    r[3] = cof(0, 1) * inv; r[4] = cof(1, 1) * inv; r[5] = cof(2, 1) * inv;
+    r[6] = cof(0, 2) * inv; r[7] = cof(1, 2) * inv; r[8] = cof(2, 2) * inv;
 }
 static void field_k(const scn_field_desc &f, FieldK &k) {
     memset(&k, 0, sizeof k);
@@ -42,7 +52,6 @@ int params_from_desc(const scn_medium_desc &d, Params &p) {
     memset(&p, 0, sizeof p);
     if (d.correlation_context < SCN_CTX_GLOBAL || d.correlation_context > SCN_CTX_NONE)
         return set_error(SCN_EINVAL, "correlation_context is mandatory (media/GaussianProcessMedium.cpp:104-106)");
-    if (d.use_aniso_mtx) return set_error(SCN_EUNSUPPORTED, "useAnisoMtx is not covered");
     if (d.cov_type < SCN_COV_SQUARED_EXPONENTIAL || d.cov_type > SCN_COV_GABOR_ISO) return set_error(SCN_EINVAL, "bad cov_type");
     const bool alt = d.cov_type >= SCN_COV_MATERN;
     if (alt) {
@@ -81,6 +90,20 @@ int params_from_desc(const scn_medium_desc &d, Params &p) {
         p.l_aniso_inv[i] = (std::isinf(inv) || std::isnan(inv)) ? 0.f : inv; // filterWithZero
     }
     p.l_aniso_max = std::fmax(std::fmax(p.l_aniso[0], p.l_aniso[1]), p.l_aniso[2]);
+    p.use_mtx = d.use_aniso_mtx != 0;
+    p.mC_dsi = 1.0;
+    for (int i = 0; i < 9; ++i) p.mL[i] = p.mW[i] = p.mC[i] = (i % 4 == 0) ? 1.f : 0.f;
+    if (p.use_mtx) { // GPF:668-675; Eigen's fixed-size inverse (cofactors) and three-term reductions x0 + (x1 + x2)
+        if (alt) return set_error(SCN_EUNSUPPORTED, "useAnisoMtx: squared-exponential kernel only");
+        for (int i = 0; i < 9; ++i) p.mL[i] = l_conv * d.aniso_mtx[i];
+        host_mat3_inverse(p.mL, p.mW);
+        for (int i = 0; i < 3; ++i) for (int j = 0; j < 3; ++j) p.mC[i * 3 + j] = p.mW[i] * p.mW[j] + (p.mW[3 + i] * p.mW[3 + j] + p.mW[6 + i] * p.mW[6 + j]);
+        const float *c = p.mC; // Eigen's bruteforce_det3_helper order
+        const float det = c[0] * (c[4] * c[8] - c[5] * c[7]) - c[1] * (c[3] * c[8] - c[5] * c[6]) + c[2] * (c[3] * c[7] - c[4] * c[6]);
+        p.mC_dsi = 1.0 / std::sqrt(det); // GPF:749: double division of a float square root (std::sqrt(float))
+        // splattingKernelRadius: max component of col0 + col1 + col2 (GPF:704-706)
+        p.l_aniso_max = std::fmax(std::fmax((p.mL[0] + p.mL[1]) + p.mL[2], (p.mL[3] + p.mL[4]) + p.mL[5]), (p.mL[6] + p.mL[7]) + p.mL[8]);
+    }
     p.ls_max = 1.f;
     if (!p.stationary && d.ls.type != SCN_FIELD_NONE) {
         const scn_field_desc &f = d.ls;

@@ -66,6 +66,10 @@ def _nonstat(multires=True, **kw):
     return c
 
 
+# a rotated, sheared anisotropy matrix (row-major), well conditioned
+_MTX_COV = {"type": "squared_exponential", "sigma": 0.05, "lengthScale": 0.1, "aniso": [1, 1, 1], "useAnisoMtx": True,
+            "anisoMtx": [1.2, 0.3, -0.1, -0.2, 0.8, 0.25, 0.15, -0.1, 1.1]}
+
 MEDIA = {
     # BASELINE.json configs
     "c1_sphere_3d_none": medium(),
@@ -116,6 +120,13 @@ MEDIA = {
     "aniso_rot_iso_const_none": medium(covariance=_nonstat(False, aniso={"type": "constant", "val": 0.35})),
     "aniso_rot_world_multires_renewal": medium(isotropic_3D_sampling=False, correlation_context="renewal", single_realization=False, impulse_density=4,
                                                covariance=_nonstat(True, aniso={"type": "noise", "noise": "front_back", "min": 0.3, "max": 0.8, "start": -1.0, "end": 1.5})),
+    # "useAnisoMtx": full anisotropy matrix of the stationary kernel (math/GPFunctions.cpp:668-675)
+    "aniso_mtx_world_renewalplus": medium(isotropic_3D_sampling=False, correlation_context="renewal+", single_realization=False,
+                                          covariance=dict(_MTX_COV)),
+    "aniso_mtx_iso_renewalplus": medium(correlation_context="renewal+", single_realization=False, covariance=dict(_MTX_COV, localScale=2.5)),
+    "aniso_mtx_1d_xy_mis": medium(correlation_context="renewal+", single_realization=False, covariance=dict(_MTX_COV),
+                                  **{"1D_sampling": True, "1D_sampling_scheme": "mis", "1D_gradient_correlationXY": True}),
+    "aniso_mtx_multires_iso": medium(correlation_context="renewal+", single_realization=False, covariance=_nonstat(True, cov=dict(_MTX_COV))),
 }
 IS_1D = {k: bool(v.get("1D_sampling")) for k, v in MEDIA.items()}
 

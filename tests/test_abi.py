@@ -79,10 +79,14 @@ def test_unsupported_configurations_are_refused_not_approximated():
     with pytest.raises(abi.ScnError) as e:
         Medium.from_json(S.medium(isotropic_3D_sampling=False, covariance={"type": "matern", "v": 2.0}))
     assert e.value.code == abi.SCN_EINVAL
-    mj = S.medium(covariance={"type": "squared_exponential", "useAnisoMtx": True})
+    # "useAnisoMtx" parses (nine numbers, row-major); a malformed matrix is a JSON error, the anisotropy field with 1D sampling is refused
+    d = Medium.desc_from_json(S.medium(covariance={"type": "squared_exponential", "useAnisoMtx": True, "anisoMtx": [1, 0.5, 0, 0, 2, 0, 0, 0, 1]}))
+    assert d.use_aniso_mtx == 1 and list(d.aniso_mtx)[:5] == [1.0, 0.5, 0.0, 0.0, 2.0]
     with pytest.raises(abi.ScnError) as e:
-        Medium.desc_from_json(mj)
-    assert e.value.code == abi.SCN_EUNSUPPORTED
+        Medium.desc_from_json(S.medium(covariance={"type": "squared_exponential", "useAnisoMtx": True, "anisoMtx": [1, 0, 0, 1]}))
+    assert e.value.code == abi.SCN_EJSON
+    d = Medium.desc_from_json(S.medium(covariance=S._nonstat(False, aniso={"type": "constant", "val": 0.3}), **{"1D_sampling": True}))
+    assert d.aniso_field.type == 1
     with pytest.raises(abi.ScnError):
         Medium.desc_from_json("{ not json")
     with pytest.raises(abi.ScnError):
