@@ -18,8 +18,9 @@
 // which hand the per-ray intermediate state (conditioning coefficients, crossing distance as a hi/lo float pair, flags) through a
 // stream-ordered scratch buffer (cudaMallocAsync on the caller's stream: no synchronisation, safe for concurrent streams).
 //
-// Covered: 1D sampling with the stationary squared-exponential kernel, 1 <= N <= 4 (compile-time), no multi-resolution.  Everything
-// else stays on the generic kernels of scn_api.cu.
+// Covered: 1D sampling with the stationary squared-exponential kernel and with its brute-force non-stationary form (BRUTE: kernel scale,
+// variance normalisation and conditioning scale follow ls(p) at the query point), 1 <= N <= 4 (compile-time), no multi-resolution.
+// Everything else stays on the generic kernels of scn_api.cu.
 #ifndef SCN_MARCH1D_CUH_
 #define SCN_MARCH1D_CUH_
 
@@ -28,7 +29,7 @@
 namespace scn {
 
 inline bool march1d_supported(const Params &P) {
-    return P.sampling_1d && P.stationary && !P.multires && !P.use_mtx && P.kernel == SCN_COV_SQUARED_EXPONENTIAL && P.n_imp >= 1 && P.n_imp <= 4;
+    return P.sampling_1d && !P.multires && !P.use_mtx && !P.has_aniso && P.kernel == SCN_COV_SQUARED_EXPONENTIAL && P.n_imp >= 1 && P.n_imp <= 4;
 }
 
 #if defined(__CUDACC__)
@@ -82,7 +83,7 @@ __global__ void __launch_bounds__(MARCH1D_BLOCK) k_cond1d(const __grid_constant_
     X.c[0][i] = c.vs; X.c[1][i] = c.gs.x; X.c[2][i] = c.gs.y; X.c[3][i] = c.gs.z; X.c[4][i] = c.org.x; X.c[5][i] = c.org.y; X.c[6][i] = c.org.z;
 }
 
-template <bool TRANSMIT, int NIMP>
+template <bool TRANSMIT, int NIMP, bool BRUTE>
 __global__ void __launch_bounds__(MARCH1D_BLOCK) k_march1d(const __grid_constant__ Params P, const MarchArgs A, const Scratch1D X) {
     const unsigned FULL = 0xffffffffu;
     const int lane = threadIdx.x & 31;
@@ -95,6 +96,7 @@ __global__ void __launch_bounds__(MARCH1D_BLOCK) k_march1d(const __grid_constant
     dbl3 o = {0, 0, 0}, rd = {0, 0, 0};
     f3 frn = F3(0, 0, 1);
     uint32_t seed = 0, evals = 0; float near_t = 0.f, oz = 0.f, cvs = 0.f, cgz = 0.f;
+    f3 corg = F3(0, 0, 0); // conditioning origin (BRUTE: the covariance scale between the point and the origin is point-dependent)
     double t = 0, pf = 0, dstep = 0, dfar = 0, intp = 0, ta = 0, t_prev = 0, t_test = 0;
     int sign0 = 1, gp_id = 0; bool first_step = false, first_scatter = true, conditioned = false;
     // register cache: a window of FOUR consecutive cells cb .. cb + 3 (an evaluation in cell i reads i - 1, i, i + 1, so the window serves
@@ -157,7 +159,8 @@ __global__ void __launch_bounds__(MARCH1D_BLOCK) k_march1d(const __grid_constant
                         conditioned = !first_scatter && cond_on;
                         if (conditioned) { // coefficients from k_cond1d; o_ray of evaluateNoise1DNormalized is constant along the ray
                             cvs = X.c[0][ri]; cgz = X.c[3][ri];
-                            oz = xdot(fr.n, xmul3(l_inv(P), F3(X.c[4][ri], X.c[5][ri], X.c[6][ri])));
+                            corg = F3(X.c[4][ri], X.c[5][ri], X.c[6][ri]);
+                            oz = xdot(fr.n, BRUTE ? cov_pos_w2l(P, corg, 1.0f) : xmul3(l_inv(P), corg));
                             evals = P.ctx == SCN_CTX_RENEWAL_PLUS ? 2u : 1u;
                         }
                         phase = PH_F0;
@@ -175,7 +178,7 @@ __global__ void __launch_bounds__(MARCH1D_BLOCK) k_march1d(const __grid_constant
             const double te = phase == PH_F0 ? (double)near_t : (phase == PH_MARCH ? t : (phase == PH_REFINE ? t_test : dfar));
             p = ray_at(o, rd, te);
             // transformPosDirWorldtoLocal (GPF:631-633; the division by localScale = 1 is exact), z of the ray frame
-            z = xdot(frn, xmul3(l_inv(P), p));
+            z = xdot(frn, BRUTE ? cov_pos_w2l(P, p, 1.0f) : xmul3(l_inv(P), p)); // BRUTE: positions carry max ls (GPF:1261-1264)
             const float tg = xdiv(z, R), fl = floorf(tg);
             frac = xsub(tg, fl); i = (int)fl;
             if (!cvalid || i < cb + 1 || i > cb + 3) nshift = 4; // new ray / jump: build cells i - 1 .. i + 2
@@ -215,6 +218,8 @@ __global__ void __launch_bounds__(MARCH1D_BLOCK) k_march1d(const __grid_constant
             for (int k = 0; k < NIMP; ++k) { im[k] = hi ? w1[k] : w0[k]; i0[k] = hi ? w2[k] : w1[k]; ip[k] = hi ? w3[k] : w2[k]; }
             const uint32_t sg = hi ? wsig >> 4 : wsig, sm = sg & 15u, s0 = (sg >> 4) & 15u, sp = (sg >> 8) & 15u;
             // noise1D (SCN:397-406): cells dx = -1, 0, +1 in this order, per-cell partial sums
+            const float lsq = BRUTE ? cov_ns_scale(P, p) : 1.0f; // the kernel's local scale at the QUERY point (SCN:425-426)
+            const float ka = BRUTE ? -0.72134752f / (lsq * lsq) : -0.72134752f;
             float sv = 0.f;
 #pragma unroll
             for (int dx = -1; dx <= 1; ++dx) {
@@ -227,16 +232,17 @@ __global__ void __launch_bounds__(MARCH1D_BLOCK) k_march1d(const __grid_constant
                     const uint32_t sb = ((dx < 0 ? sm : (dx == 0 ? s0 : sp)) >> k) & 1u;
                     const float tp = xsub(tc, tik);
                     const float ab = xsub(Rtc, xmul(R, tik));
-                    float kv = ex2_approx(-0.72134752f * ab * ab); // exp(-ab^2 / 2): splattingKernel1DVal with localScale 1 (GPF:835-841)
+                    float kv = ex2_approx(ka * ab * ab); // exp(-ab^2 / (2 ls^2)): splattingKernel1DVal (GPF:835-841)
                     kv = xmul(tp, tp) < 1.0f ? kv : 0.f;
                     cv += sb ? kv : -kv;
                 }
                 sv += cv;
             }
-            float nv = sv / nf; // SCN:334-336
+            float nv = sv / (BRUTE ? sqrtf(se_variance1d(P, R, lsq)) : nf); // SCN:334-336
             if (conditioned) { // SCN:338-357 with kernelSpatialScale = 1, stationary covariance
                 const float ab = z - oz;
-                nv += 1.0f * (cvs * se_c1d_val(ab, 1.0f) + (1.0f * cgz) * se_c1d_grad(ab, 1.0f));
+                const float cls = BRUTE ? cov_splat_cov1d(P, p, corg) : 1.0f;
+                nv += 1.0f * (cvs * se_c1d_val(ab, cls) + (1.0f * cgz) * se_c1d_grad(ab, cls));
             }
             const float amp = cov_amplitude(P, p);
             double mean; gp_mean_and_id(P, p, mean, id);
@@ -331,13 +337,22 @@ inline cudaError_t launch_march1d_t(const Params &P, const MarchArgs &A, int sm_
     const Scratch1D X = scratch1d_carve(scratch, A.n);
     const unsigned per_ray_grid = (A.n + MARCH1D_BLOCK - 1) / MARCH1D_BLOCK;
     if (P.activate_conditioning) k_cond1d<<<per_ray_grid, MARCH1D_BLOCK, 0, s>>>(P, A.r, A.s, X, A.n);
-    unsigned grid = (unsigned)(sm_count * 4); if (grid > per_ray_grid) grid = per_ray_grid;
+    const bool brute = !P.stationary;
+    auto launch = [&](auto kern) -> cudaError_t {
+        int per_sm = 0; // resident blocks per SM (registers): one wave of persistent blocks
+        cudaError_t er = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, MARCH1D_BLOCK, 0);
+        if (er != cudaSuccess) return er;
+        unsigned grid = (unsigned)(sm_count * (per_sm < 1 ? 1 : per_sm)); if (grid > per_ray_grid) grid = per_ray_grid;
+        kern<<<grid, MARCH1D_BLOCK, 0, s>>>(P, A, X);
+        return cudaSuccess;
+    };
     switch (P.n_imp) {
-    case 1: k_march1d<TRANSMIT, 1><<<grid, MARCH1D_BLOCK, 0, s>>>(P, A, X); break;
-    case 2: k_march1d<TRANSMIT, 2><<<grid, MARCH1D_BLOCK, 0, s>>>(P, A, X); break;
-    case 3: k_march1d<TRANSMIT, 3><<<grid, MARCH1D_BLOCK, 0, s>>>(P, A, X); break;
-    default: k_march1d<TRANSMIT, 4><<<grid, MARCH1D_BLOCK, 0, s>>>(P, A, X); break;
+    case 1: e = brute ? launch(k_march1d<TRANSMIT, 1, true>) : launch(k_march1d<TRANSMIT, 1, false>); break;
+    case 2: e = brute ? launch(k_march1d<TRANSMIT, 2, true>) : launch(k_march1d<TRANSMIT, 2, false>); break;
+    case 3: e = brute ? launch(k_march1d<TRANSMIT, 3, true>) : launch(k_march1d<TRANSMIT, 3, false>); break;
+    default: e = brute ? launch(k_march1d<TRANSMIT, 4, true>) : launch(k_march1d<TRANSMIT, 4, false>); break;
     }
+    if (e != cudaSuccess) { cudaFreeAsync(scratch, s); return e; }
     if (!TRANSMIT) k_finish1d<<<per_ray_grid, MARCH1D_BLOCK, 0, s>>>(P, A, X);
     e = cudaGetLastError();
     cudaError_t e2 = cudaFreeAsync(scratch, s);

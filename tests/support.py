@@ -120,6 +120,8 @@ MEDIA = {
     "aniso_rot_iso_const_none": medium(covariance=_nonstat(False, aniso={"type": "constant", "val": 0.35})),
     "aniso_rot_world_multires_renewal": medium(isotropic_3D_sampling=False, correlation_context="renewal", single_realization=False, impulse_density=4,
                                                covariance=_nonstat(True, aniso={"type": "noise", "noise": "front_back", "min": 0.3, "max": 0.8, "start": -1.0, "end": 1.5})),
+    "nonstat_bruteforce_1d_renewalplus": medium(correlation_context="renewal+", single_realization=False, covariance=_nonstat(False),
+                                                **{"1D_sampling": True, "1D_sampling_scheme": "mis"}),  # (correlationXY is not defined for brute force: SCN warns)
     # "useAnisoMtx": full anisotropy matrix of the stationary kernel (math/GPFunctions.cpp:668-675)
     "aniso_mtx_world_renewalplus": medium(isotropic_3D_sampling=False, correlation_context="renewal+", single_realization=False,
                                           covariance=dict(_MTX_COV)),
