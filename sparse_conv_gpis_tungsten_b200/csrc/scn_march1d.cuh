@@ -19,7 +19,8 @@
 // stream-ordered scratch buffer (cudaMallocAsync on the caller's stream: no synchronisation, safe for concurrent streams).
 //
 // Covered: 1D sampling with the stationary squared-exponential kernel and with its brute-force non-stationary form (BRUTE: kernel scale,
-// variance normalisation and conditioning scale follow ls(p) at the query point), 1 <= N <= 4 (compile-time), no multi-resolution.
+// variance normalisation and conditioning scale follow ls(p) at the query point) and its multi-resolution form (two levels, each with its
+// own register window), 1 <= N <= 4 (compile-time).
 // Everything else stays on the generic kernels of scn_api.cu.
 #ifndef SCN_MARCH1D_CUH_
 #define SCN_MARCH1D_CUH_
@@ -29,7 +30,7 @@
 namespace scn {
 
 inline bool march1d_supported(const Params &P) {
-    return P.sampling_1d && !P.multires && !P.use_mtx && !P.has_aniso && P.kernel == SCN_COV_SQUARED_EXPONENTIAL && P.n_imp >= 1 && P.n_imp <= 4;
+    return P.sampling_1d && !P.use_mtx && !P.has_aniso && P.kernel == SCN_COV_SQUARED_EXPONENTIAL && P.n_imp >= 1 && P.n_imp <= 4;
 }
 
 #if defined(__CUDACC__)
@@ -47,6 +48,81 @@ __device__ __forceinline__ void cell1d_generate(uint32_t cell, uint32_t seed, fl
         const float ws = g.next();
         plus |= (ws < 0.5f ? 0u : 1u) << k; // Bernoulli: rv < 0.5 ? -1 : +1 (math/MathUtil.hpp:226-228)
     }
+}
+
+// Register cache of one lattice level: a window of FOUR consecutive cells cb .. cb + 3 (an evaluation in cell i reads i - 1, i, i + 1, so
+// the window serves i = cb + 1 and i = cb + 2).  The spare cell is what lets the regeneration run converged: a lane MUST move its window
+// when it enters cb + 3, and whenever any lane of the warp must, every lane already in cb + 2 moves too (one cell early).  After such a
+// round every lane is at least one full cell away from its next forced move, so rounds happen about once per cell length (~21 steps) with
+// most lanes taking part, instead of each lane regenerating on its own iteration with one or two lanes active.
+template <int NIMP>
+struct Win1D { int cb, ck; bool valid; float w0[NIMP], w1[NIMP], w2[NIMP], w3[NIMP]; uint32_t sig; /* sign bits: 4 per slot */ };
+
+// noise1D (SCN:397-406) for this lane's point (cell i, fraction frac) of the level with table index kidx and seed seedl, through the
+// window; `ka` = -log2(e) / (2 ls^2).  Called by all 32 lanes together (window moves are warp-cooperative); returns the unnormalised sum.
+template <int NIMP>
+__device__ __forceinline__ float win1d_noise(Win1D<NIMP> &W, const bool active, const int i, const float frac, const uint32_t seedl, const int kidx,
+                                             const float R, const float ka, const int lane) {
+    const unsigned FULL = 0xffffffffu;
+    int nshift = 0; bool must = false;
+    if (active) {
+        if (!W.valid || W.ck != kidx || i < W.cb + 1 || i > W.cb + 3) nshift = 4; // new ray / level change / jump: build cells i - 1 .. i + 2
+        else if (i == W.cb + 3) { nshift = 1; must = true; }
+        else if (i == W.cb + 2) nshift = 1; // one cell early, taken only when some lane of the warp must move
+    }
+    // a lane that starts a ray (or jumped): lanes 0..3 generate its four cells side by side and hand them over by shuffles
+    unsigned ms = __ballot_sync(FULL, nshift == 4);
+    while (ms) {
+        const int T = __ffs(ms) - 1; ms &= ms - 1;
+        const int ti = __shfl_sync(FULL, i, T); const uint32_t ts = __shfl_sync(FULL, seedl, T);
+        float g[NIMP]; uint32_t plus = 0u;
+#pragma unroll
+        for (int k = 0; k < NIMP; ++k) g[k] = 0.f;
+        if (lane < 4) cell1d_generate<NIMP>((uint32_t)(ti - 1 + lane), ts, g, plus);
+#pragma unroll
+        for (int k = 0; k < NIMP; ++k) {
+            const float a0 = __shfl_sync(FULL, g[k], 0), a1 = __shfl_sync(FULL, g[k], 1), a2 = __shfl_sync(FULL, g[k], 2), a3 = __shfl_sync(FULL, g[k], 3);
+            if (lane == T) { W.w0[k] = a0; W.w1[k] = a1; W.w2[k] = a2; W.w3[k] = a3; }
+        }
+        const uint32_t pw = __shfl_sync(FULL, plus, 0) | (__shfl_sync(FULL, plus, 1) << 4) | (__shfl_sync(FULL, plus, 2) << 8) | (__shfl_sync(FULL, plus, 3) << 12);
+        if (lane == T) { W.sig = pw; W.cb = ti - 1; W.ck = kidx; W.valid = true; }
+    }
+    if (__any_sync(FULL, must)) { // a round: every lane in the upper half of its window moves one cell forward
+        if (nshift == 1) {
+#pragma unroll
+            for (int k = 0; k < NIMP; ++k) { W.w0[k] = W.w1[k]; W.w1[k] = W.w2[k]; W.w2[k] = W.w3[k]; }
+            W.cb += 1;
+            uint32_t plus; cell1d_generate<NIMP>((uint32_t)(W.cb + 3), seedl, W.w3, plus);
+            W.sig = (W.sig >> 4) | (plus << 12);
+        }
+    }
+    float sv = 0.f;
+    if (active) {
+        const bool hi = i == W.cb + 2; // which three of the four cached cells are i - 1, i, i + 1
+        float im[NIMP], i0[NIMP], ip[NIMP];
+#pragma unroll
+        for (int k = 0; k < NIMP; ++k) { im[k] = hi ? W.w1[k] : W.w0[k]; i0[k] = hi ? W.w2[k] : W.w1[k]; ip[k] = hi ? W.w3[k] : W.w2[k]; }
+        const uint32_t sg = hi ? W.sig >> 4 : W.sig, sm = sg & 15u, s0 = (sg >> 4) & 15u, sp = (sg >> 8) & 15u;
+        // cells dx = -1, 0, +1 in this order, per-cell partial sums; the rejection test on the reference's operands
+#pragma unroll
+        for (int dx = -1; dx <= 1; ++dx) {
+            const float tc = xsub(frac, (float)dx);
+            const float Rtc = xmul(R, tc);
+            float cv = 0.f;
+#pragma unroll
+            for (int k = 0; k < NIMP; ++k) {
+                const float tik = dx < 0 ? im[k] : (dx == 0 ? i0[k] : ip[k]);
+                const uint32_t sb = ((dx < 0 ? sm : (dx == 0 ? s0 : sp)) >> k) & 1u;
+                const float tp = xsub(tc, tik);
+                const float ab = xsub(Rtc, xmul(R, tik));
+                float kv = ex2_approx(ka * ab * ab); // exp(-ab^2 / (2 ls^2)): splattingKernel1DVal (GPF:835-841)
+                kv = xmul(tp, tp) < 1.0f ? kv : 0.f;
+                cv += sb ? kv : -kv;
+            }
+            sv += cv;
+        }
+    }
+    return sv;
 }
 
 // per-ray intermediate state between the three kernels (device scratch, n elements per array)
@@ -83,7 +159,8 @@ __global__ void __launch_bounds__(MARCH1D_BLOCK) k_cond1d(const __grid_constant_
     X.c[0][i] = c.vs; X.c[1][i] = c.gs.x; X.c[2][i] = c.gs.y; X.c[3][i] = c.gs.z; X.c[4][i] = c.org.x; X.c[5][i] = c.org.y; X.c[6][i] = c.org.z;
 }
 
-template <bool TRANSMIT, int NIMP, bool BRUTE>
+// VAR: 0 = stationary kernel, 1 = brute-force non-stationary (point-dependent kernel scale), 2 = multi-resolution (two levels, SCN:126-135)
+template <bool TRANSMIT, int NIMP, int VAR>
 __global__ void __launch_bounds__(MARCH1D_BLOCK) k_march1d(const __grid_constant__ Params P, const MarchArgs A, const Scratch1D X) {
     const unsigned FULL = 0xffffffffu;
     const int lane = threadIdx.x & 31;
@@ -91,6 +168,8 @@ __global__ void __launch_bounds__(MARCH1D_BLOCK) k_march1d(const __grid_constant
     const bool absorb = !TRANSMIT && P.absorption_only;
     const bool cond_on = P.activate_conditioning != 0;
     const float R = P.R_iso, nf = P.nf_1d;
+    constexpr bool BRUTE = VAR == 1, MULTI = VAR == 2;
+    constexpr int NLEV = MULTI ? 2 : 1;
 
     int phase = PH_FETCH; unsigned ri = 0;
     dbl3 o = {0, 0, 0}, rd = {0, 0, 0};
@@ -99,15 +178,14 @@ __global__ void __launch_bounds__(MARCH1D_BLOCK) k_march1d(const __grid_constant
     f3 corg = F3(0, 0, 0); // conditioning origin (BRUTE: the covariance scale between the point and the origin is point-dependent)
     double t = 0, pf = 0, dstep = 0, dfar = 0, intp = 0, ta = 0, t_prev = 0, t_test = 0;
     int sign0 = 1, gp_id = 0; bool first_step = false, first_scatter = true, conditioned = false;
-    // register cache: a window of FOUR consecutive cells cb .. cb + 3 (an evaluation in cell i reads i - 1, i, i + 1, so the window serves
-    // i = cb + 1 and i = cb + 2).  The spare cell is what lets the regeneration run converged: a lane MUST move its window when it enters
-    // cb + 3, and whenever any lane of the warp must, every lane already in cb + 2 moves too (one cell early).  After such a round every
-    // lane is at least one full cell away from its next forced move, so rounds happen about once per cell length (~21 steps) with most
-    // lanes taking part, instead of each lane regenerating on its own iteration with one or two lanes active.
-    int cb = 0; bool cvalid = false;
-    float w0[NIMP], w1[NIMP], w2[NIMP], w3[NIMP]; uint32_t wsig = 0u; // sign bits: 4 per slot
+    float osf_lo = 1.f, osf_hi = 1.f; // MULTI: blend weights of the conditioning origin's two levels (SCN:340-343)
+    Win1D<NIMP> W[NLEV];
 #pragma unroll
-    for (int k = 0; k < NIMP; ++k) { w0[k] = 0.f; w1[k] = 0.f; w2[k] = 0.f; w3[k] = 0.f; }
+    for (int l = 0; l < NLEV; ++l) {
+        W[l].cb = 0; W[l].ck = 0; W[l].valid = false; W[l].sig = 0u;
+#pragma unroll
+        for (int k = 0; k < NIMP; ++k) { W[l].w0[k] = 0.f; W[l].w1[k] = 0.f; W[l].w2[k] = 0.f; W[l].w3[k] = 0.f; }
+    }
 
     for (;;) {
         // ------------------------------------------------------------ fetch rays for idle lanes (warp-aggregated atomic)
@@ -155,12 +233,14 @@ __global__ void __launch_bounds__(MARCH1D_BLOCK) k_march1d(const __grid_constant
                         if (P.step_size < step) step = P.step_size;
                         dstep = (double)step; dfar = (double)far_t;
                         t = (double)xadd(near_t, xmul(step, u)); // SCNM:129
-                        cvalid = false;
+#pragma unroll
+                        for (int l = 0; l < NLEV; ++l) W[l].valid = false;
                         conditioned = !first_scatter && cond_on;
                         if (conditioned) { // coefficients from k_cond1d; o_ray of evaluateNoise1DNormalized is constant along the ray
                             cvs = X.c[0][ri]; cgz = X.c[3][ri];
                             corg = F3(X.c[4][ri], X.c[5][ri], X.c[6][ri]);
                             oz = xdot(fr.n, BRUTE ? cov_pos_w2l(P, corg, 1.0f) : xmul3(l_inv(P), corg));
+                            if (MULTI) { const Levels oi = level_ratio(P, corg); osf_lo = oi.r_lo; osf_hi = oi.r_hi; }
                             evals = P.ctx == SCN_CTX_RENEWAL_PLUS ? 2u : 1u;
                         }
                         phase = PH_F0;
@@ -173,77 +253,43 @@ __global__ void __launch_bounds__(MARCH1D_BLOCK) k_march1d(const __grid_constant
 
         // ------------------------------------------------------------ evaluateValue (SCN:73-89) through the register cache
         float fval = 0.f; int id = 0;
-        f3 p = F3(0.f, 0.f, 0.f); float z = 0.f, frac = 0.f; int i = 0, nshift = 0; bool must = false;
+        f3 p = F3(0.f, 0.f, 0.f);
         if (active) {
             const double te = phase == PH_F0 ? (double)near_t : (phase == PH_MARCH ? t : (phase == PH_REFINE ? t_test : dfar));
             p = ray_at(o, rd, te);
-            // transformPosDirWorldtoLocal (GPF:631-633; the division by localScale = 1 is exact), z of the ray frame
-            z = xdot(frn, BRUTE ? cov_pos_w2l(P, p, 1.0f) : xmul3(l_inv(P), p)); // BRUTE: positions carry max ls (GPF:1261-1264)
-            const float tg = xdiv(z, R), fl = floorf(tg);
-            frac = xsub(tg, fl); i = (int)fl;
-            if (!cvalid || i < cb + 1 || i > cb + 3) nshift = 4; // new ray / jump: build cells i - 1 .. i + 2
-            else if (i == cb + 3) { nshift = 1; must = true; }
-            else if (i == cb + 2) nshift = 1; // one cell early, taken only when some lane of the warp must move
         }
-        // a lane that starts a ray (or jumped): lanes 0..3 generate its four cells side by side and hand them over by shuffles
-        unsigned ms = __ballot_sync(FULL, nshift == 4);
-        while (ms) {
-            const int T = __ffs(ms) - 1; ms &= ms - 1;
-            const int ti = __shfl_sync(FULL, i, T); const uint32_t ts = __shfl_sync(FULL, seed, T);
-            float g[NIMP]; uint32_t plus = 0u;
+        Levels L; L.s_lo = L.s_hi = 1.f; L.r_lo = 1.f; L.r_hi = 0.f; L.k_lo = 0;
+        if (MULTI && active) L = level_ratio(P, p);
+        const float lsq = (BRUTE && active) ? cov_ns_scale(P, p) : 1.0f; // the kernel's local scale at the QUERY point (SCN:425-426)
+        const float ka = BRUTE ? -0.72134752f / (lsq * lsq) : -0.72134752f;
+        float nv = 0.f;
 #pragma unroll
-            for (int k = 0; k < NIMP; ++k) g[k] = 0.f;
-            if (lane < 4) cell1d_generate<NIMP>((uint32_t)(ti - 1 + lane), ts, g, plus);
-#pragma unroll
-            for (int k = 0; k < NIMP; ++k) {
-                const float a0 = __shfl_sync(FULL, g[k], 0), a1 = __shfl_sync(FULL, g[k], 1), a2 = __shfl_sync(FULL, g[k], 2), a3 = __shfl_sync(FULL, g[k], 3);
-                if (lane == T) { w0[k] = a0; w1[k] = a1; w2[k] = a2; w3[k] = a3; }
+        for (int l = 0; l < NLEV; ++l) {
+            const float kss = MULTI ? (l ? L.s_hi : L.s_lo) : 1.0f;
+            const int kidx = MULTI ? L.k_lo + l : 0;
+            const uint32_t seedl = seed + (uint32_t)(MULTI ? P.lvl_add_seed[kidx] : 0);
+            // transformPosDirWorldtoLocal (GPF:631-633; stationary: the division by 1 is exact; BRUTE: max ls; MULTI: the level's scale), z of the ray frame
+            float z = 0.f, frac = 0.f; int i = 0;
+            if (active) {
+                z = xdot(frn, MULTI ? xdiv3(xmul3(l_inv(P), p), kss) : (BRUTE ? cov_pos_w2l(P, p, 1.0f) : xmul3(l_inv(P), p)));
+                const float tg = xdiv(z, R), fl = floorf(tg);
+                frac = xsub(tg, fl); i = (int)fl;
             }
-            const uint32_t pw = __shfl_sync(FULL, plus, 0) | (__shfl_sync(FULL, plus, 1) << 4) | (__shfl_sync(FULL, plus, 2) << 8) | (__shfl_sync(FULL, plus, 3) << 12);
-            if (lane == T) { wsig = pw; cb = ti - 1; cvalid = true; }
-        }
-        if (__any_sync(FULL, must)) { // a round: every lane in the upper half of its window moves one cell forward
-            if (nshift == 1) {
-#pragma unroll
-                for (int k = 0; k < NIMP; ++k) { w0[k] = w1[k]; w1[k] = w2[k]; w2[k] = w3[k]; }
-                cb += 1;
-                uint32_t plus; cell1d_generate<NIMP>((uint32_t)(cb + 3), seed, w3, plus);
-                wsig = (wsig >> 4) | (plus << 12);
+            const float sv = win1d_noise<NIMP>(W[l], active, i, frac, seedl, kidx, R, ka, lane);
+            float nl = 0.f;
+            if (active) {
+                nl = sv / (BRUTE ? sqrtf(se_variance1d(P, R, lsq)) : nf); // SCN:334-336
+                if (conditioned) { // SCN:338-357
+                    const float ozl = MULTI ? xdot(frn, xdiv3(xmul3(l_inv(P), corg), kss)) : oz;
+                    const float ab = z - ozl;
+                    const float cls = BRUTE ? cov_splat_cov1d(P, p, corg) : 1.0f;
+                    const float osf = MULTI ? (l ? osf_hi : osf_lo) : 1.0f;
+                    nl += osf * (cvs * se_c1d_val(ab, cls) + (kss * cgz) * se_c1d_grad(ab, cls));
+                }
             }
+            nv = MULTI ? nv + (l ? L.r_hi : L.r_lo) * nl : nl; // SCN:131-134
         }
         if (active) {
-            const bool hi = i == cb + 2; // which three of the four cached cells are i - 1, i, i + 1
-            float im[NIMP], i0[NIMP], ip[NIMP];
-#pragma unroll
-            for (int k = 0; k < NIMP; ++k) { im[k] = hi ? w1[k] : w0[k]; i0[k] = hi ? w2[k] : w1[k]; ip[k] = hi ? w3[k] : w2[k]; }
-            const uint32_t sg = hi ? wsig >> 4 : wsig, sm = sg & 15u, s0 = (sg >> 4) & 15u, sp = (sg >> 8) & 15u;
-            // noise1D (SCN:397-406): cells dx = -1, 0, +1 in this order, per-cell partial sums
-            const float lsq = BRUTE ? cov_ns_scale(P, p) : 1.0f; // the kernel's local scale at the QUERY point (SCN:425-426)
-            const float ka = BRUTE ? -0.72134752f / (lsq * lsq) : -0.72134752f;
-            float sv = 0.f;
-#pragma unroll
-            for (int dx = -1; dx <= 1; ++dx) {
-                const float tc = xsub(frac, (float)dx);
-                const float Rtc = xmul(R, tc);
-                float cv = 0.f;
-#pragma unroll
-                for (int k = 0; k < NIMP; ++k) {
-                    const float tik = dx < 0 ? im[k] : (dx == 0 ? i0[k] : ip[k]);
-                    const uint32_t sb = ((dx < 0 ? sm : (dx == 0 ? s0 : sp)) >> k) & 1u;
-                    const float tp = xsub(tc, tik);
-                    const float ab = xsub(Rtc, xmul(R, tik));
-                    float kv = ex2_approx(ka * ab * ab); // exp(-ab^2 / (2 ls^2)): splattingKernel1DVal (GPF:835-841)
-                    kv = xmul(tp, tp) < 1.0f ? kv : 0.f;
-                    cv += sb ? kv : -kv;
-                }
-                sv += cv;
-            }
-            float nv = sv / (BRUTE ? sqrtf(se_variance1d(P, R, lsq)) : nf); // SCN:334-336
-            if (conditioned) { // SCN:338-357 with kernelSpatialScale = 1, stationary covariance
-                const float ab = z - oz;
-                const float cls = BRUTE ? cov_splat_cov1d(P, p, corg) : 1.0f;
-                nv += 1.0f * (cvs * se_c1d_val(ab, cls) + (1.0f * cgz) * se_c1d_grad(ab, cls));
-            }
             const float amp = cov_amplitude(P, p);
             double mean; gp_mean_and_id(P, p, mean, id);
             if (P.surf_vol_sep) id = 1.f < P.surf_vol_thresh ? 0 : 1;
@@ -337,7 +383,7 @@ inline cudaError_t launch_march1d_t(const Params &P, const MarchArgs &A, int sm_
     const Scratch1D X = scratch1d_carve(scratch, A.n);
     const unsigned per_ray_grid = (A.n + MARCH1D_BLOCK - 1) / MARCH1D_BLOCK;
     if (P.activate_conditioning) k_cond1d<<<per_ray_grid, MARCH1D_BLOCK, 0, s>>>(P, A.r, A.s, X, A.n);
-    const bool brute = !P.stationary;
+    const int var = P.multires ? 2 : (P.stationary ? 0 : 1);
     auto launch = [&](auto kern) -> cudaError_t {
         int per_sm = 0; // resident blocks per SM (registers): one wave of persistent blocks
         cudaError_t er = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, MARCH1D_BLOCK, 0);
@@ -346,12 +392,14 @@ inline cudaError_t launch_march1d_t(const Params &P, const MarchArgs &A, int sm_
         kern<<<grid, MARCH1D_BLOCK, 0, s>>>(P, A, X);
         return cudaSuccess;
     };
+#define SCN_M1D(N) (var == 2 ? launch(k_march1d<TRANSMIT, N, 2>) : (var == 1 ? launch(k_march1d<TRANSMIT, N, 1>) : launch(k_march1d<TRANSMIT, N, 0>)))
     switch (P.n_imp) {
-    case 1: e = brute ? launch(k_march1d<TRANSMIT, 1, true>) : launch(k_march1d<TRANSMIT, 1, false>); break;
-    case 2: e = brute ? launch(k_march1d<TRANSMIT, 2, true>) : launch(k_march1d<TRANSMIT, 2, false>); break;
-    case 3: e = brute ? launch(k_march1d<TRANSMIT, 3, true>) : launch(k_march1d<TRANSMIT, 3, false>); break;
-    default: e = brute ? launch(k_march1d<TRANSMIT, 4, true>) : launch(k_march1d<TRANSMIT, 4, false>); break;
+    case 1: e = SCN_M1D(1); break;
+    case 2: e = SCN_M1D(2); break;
+    case 3: e = SCN_M1D(3); break;
+    default: e = SCN_M1D(4); break;
     }
+#undef SCN_M1D
     if (e != cudaSuccess) { cudaFreeAsync(scratch, s); return e; }
     if (!TRANSMIT) k_finish1d<<<per_ray_grid, MARCH1D_BLOCK, 0, s>>>(P, A, X);
     e = cudaGetLastError();

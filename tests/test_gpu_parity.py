@@ -169,7 +169,7 @@ def test_march_round_trip_properties(torch_cuda):
 
 @pytest.mark.parametrize("secondary", [False, True])
 @pytest.mark.parametrize("name", ["c1_sphere_3d_none", "c3_1d_renewal", "c4_1d_renewalplus_xy_mis", "c5_multires_nonstat_renewalplus", "iso_3d_renewalplus_aniso",
-                                  "world_3d_renewalplus", "multires_world", "nonstat_bruteforce_iso", "nonstat_bruteforce_world_var", "nonstat_bruteforce_1d_renewalplus"])
+                                  "world_3d_renewalplus", "multires_world", "nonstat_bruteforce_iso", "nonstat_bruteforce_world_var", "nonstat_bruteforce_1d_renewalplus", "multires_1d_xy", "multires_1d_renewal"])
 def test_march_kernels_vs_oracle_8k_rays(torch_cuda, name, secondary):
     """The cached march kernels (k_march in its iso-ray and world modes, stationary / brute-force / multi-resolution; k_march1d) against the CPU oracle on 8192 seeded rays per medium,
     primary (camera) and secondary (conditioned, Renewal state carried in) wavefronts: decisions identical up to the zero-crossing
