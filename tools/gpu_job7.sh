@@ -1,4 +1,4 @@
-# full GPU job: parity tests, smoke, bench (both arms), launch list, ncu captures of the hot kernels
+# full GPU job, part A: parity tests, smoke, bench (both arms), launch list, ncu capture of the roofline kernel
 set -x; mkdir -p gpurun_out; T=${TAG:-v30}
 python -m pytest tests -m gpu -q 2>&1 | tail -3 > gpurun_out/pytest_$T.log; cat gpurun_out/pytest_$T.log
 python -c "import __graft_entry__ as g; g.smoke()" 2>&1 | tail -2
@@ -13,7 +13,4 @@ for k,v in d['extra'].items():
 PY
 ncu --metrics gpu__time_duration.sum --clock-control none -c 900 --csv --log-file gpurun_out/launches_$T.csv python bench.py --steps 2 --warmup 3 --e2e-points 4194304 > gpurun_out/ncu_launches_$T.log 2>&1
 ncu --set full --clock-control none --import-source on -k regex:k_fast_noise3d --launch-skip 2 -c 1 -f -o gpurun_out/fast_$T python bench.py --steps 2 --warmup 3 --no-extras --e2e-points 4194304 > gpurun_out/ncu_fast_$T.log 2>&1
-ncu --set full --clock-control none --import-source on -k regex:k_march --launch-skip 1 -c 1 -f -o gpurun_out/march_c1_$T python tools/run_queries.py c1_sphere_3d_none 20 1 > gpurun_out/ncu_march_c1_$T.log 2>&1
-ncu --set full --clock-control none --import-source on -k regex:k_march --launch-skip 1 -c 1 -f -o gpurun_out/march_c5_$T python tools/run_queries.py c5_multires_nonstat_renewalplus 20 1 > gpurun_out/ncu_march_c5_$T.log 2>&1
-ncu --set full --clock-control none --import-source on -k regex:k_march1d --launch-skip 1 -c 1 -f -o gpurun_out/march1d_$T python tools/run_queries.py c3_1d_renewal 20 1 > gpurun_out/ncu_march1d_$T.log 2>&1
 ls -la gpurun_out | tail -6
