@@ -395,7 +395,7 @@ def run_gpu(args):
             "clocks": clocks, "roofline": roofline,
             "cpu_baseline": {"value": cpu_v, "unit": UNIT, "cores": threads, "kind": kind, "sample": "first 2^22 of the 2^26 points, value+gradient, one pass"},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": 24 * ne, "d2h_bytes_per_step": 16 * ne, "points_per_step": ne,
-                    "api": "scn_eval_batch_host (pinned host buffers, 3-stream chunked pipeline)"},
+                    "api": "scn_eval_batch_host (pinned host buffers; H2D, kernel and D2H each on their own stream, chunks chained by events)"},
             "gpu_launches": args.steps, "extra": extra}
     if world > 1:
         dist.destroy_process_group()

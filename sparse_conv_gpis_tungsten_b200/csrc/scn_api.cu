@@ -176,6 +176,7 @@ struct scn_medium {
     cudaStream_t streams[3] = {nullptr, nullptr, nullptr};
     char *arena[3] = {nullptr, nullptr, nullptr};
     size_t arena_cap = 0;
+    cudaEvent_t ev_in[3] = {nullptr, nullptr, nullptr}, ev_k[3] = {nullptr, nullptr, nullptr}, ev_out[3] = {nullptr, nullptr, nullptr};
     // k_march: ring of ray counters (one per launch in flight, zeroed in-stream before the launch) and the SM count
     static constexpr unsigned COUNTERS = 1024;
     unsigned int *counters = nullptr;
@@ -255,7 +256,8 @@ void scn_medium_destroy(scn_medium *m) {
     if (!m) return;
     {
         DeviceGuard g(m->device);
-        for (int i = 0; i < 3; ++i) { if (m->arena[i]) cudaFree(m->arena[i]); if (m->streams[i]) cudaStreamDestroy(m->streams[i]); }
+        for (int i = 0; i < 3; ++i) { if (m->arena[i]) cudaFree(m->arena[i]); if (m->streams[i]) cudaStreamDestroy(m->streams[i]);
+                                      if (m->ev_in[i]) cudaEventDestroy(m->ev_in[i]); if (m->ev_k[i]) cudaEventDestroy(m->ev_k[i]); if (m->ev_out[i]) cudaEventDestroy(m->ev_out[i]); }
         if (m->counters) cudaFree(m->counters);
     }
     delete m;
@@ -407,6 +409,10 @@ int scn_debug_accepted_counts(const scn_medium *m, const float *px, const float 
 // chunk k+1, the kernel of chunk k and the D2H copy of chunk k-1 overlap.  The arena is grown once and reused.
 static int ensure_arena(scn_medium *m, size_t bytes_per_slot) {
     for (int i = 0; i < 3; ++i) if (!m->streams[i]) SCN_CUDA(cudaStreamCreateWithFlags(&m->streams[i], cudaStreamNonBlocking));
+    for (int i = 0; i < 3; ++i) if (!m->ev_out[i]) {
+        SCN_CUDA(cudaEventCreateWithFlags(&m->ev_in[i], cudaEventDisableTiming)); SCN_CUDA(cudaEventCreateWithFlags(&m->ev_k[i], cudaEventDisableTiming));
+        SCN_CUDA(cudaEventCreateWithFlags(&m->ev_out[i], cudaEventDisableTiming));
+    }
     if (bytes_per_slot <= m->arena_cap) return SCN_OK;
     for (int i = 0; i < 3; ++i) { if (m->arena[i]) { SCN_CUDA(cudaFree(m->arena[i])); m->arena[i] = nullptr; } }
     m->arena_cap = 0;
@@ -414,7 +420,16 @@ static int ensure_arena(scn_medium *m, size_t bytes_per_slot) {
     m->arena_cap = bytes_per_slot;
     return SCN_OK;
 }
-constexpr size_t HOST_CHUNK = (size_t)1 << 21; // queries per pipeline stage
+// Queries per pipeline stage of the *_host entry points: at most 2^22 (SCN_HOST_CHUNK_LOG2 = 16..24 overrides the cap for tuning on a
+// given host), at least 2^16, and small enough that a batch makes eight stages, so that mid-sized batches overlap their copies too.
+static size_t host_chunk(size_t n) {
+    const char *e = getenv("SCN_HOST_CHUNK_LOG2"); int l = e ? atoi(e) : 22;
+    const size_t cap = (size_t)1 << (l < 16 ? 16 : (l > 24 ? 24 : l));
+    size_t c = ((n + 7) / 8 + 255) & ~(size_t)255;
+    if (c < ((size_t)1 << 16)) c = (size_t)1 << 16;
+    if (c > cap) c = cap;
+    return c < n ? c : n;
+}
 
 } // extern "C"
 struct Carver { // carves aligned sub-buffers out of one arena slot
@@ -431,34 +446,45 @@ int scn_eval_batch_host(scn_medium *m, const scn_eval_in *in, const scn_eval_out
     if (!in->px || !in->py || !in->pz || !in->dx || !in->dy || !in->dz) return set_error(SCN_EINVAL, "eval: points and directions are required");
     std::lock_guard<std::mutex> lock(m->mu);
     DeviceGuard g(m->device); if (!g.ok) return set_error(SCN_ECUDA, "cannot select device %d", m->device);
-    size_t chunk = n < HOST_CHUNK ? n : HOST_CHUNK;
+    size_t chunk = host_chunk(n);
     size_t per = ((chunk * 4 + 255) & ~(size_t)255) * 32; // <= 32 arrays of 4-byte elements
     if (int rc = ensure_arena(m, per)) return rc;
     bool has_ctx = true; for (int i = 0; i < 7; ++i) has_ctx = has_ctx && in->ctx[i];
-    int slot = 0;
-    for (size_t b = 0; b < n; b += chunk, slot = (slot + 1) % 3) {
+    // One stream per stage: every H2D copy on `up`, every kernel on `run`, every D2H copy on `down`, chained by events per arena slot,
+    // so that each copy engine sees its transfers back to back in batch order and the two directions stay busy at once.
+    cudaStream_t up = m->streams[0], run = m->streams[1], down = m->streams[2];
+    int slot = 0; size_t k = 0;
+    for (size_t b = 0; b < n; b += chunk, slot = (slot + 1) % 3, ++k) {
         size_t c = n - b < chunk ? n - b : chunk;
-        cudaStream_t s = m->streams[slot];
+        cudaStream_t s = up;
         Carver cv{m->arena[slot]};
         scn_eval_in di = *in; scn_eval_out dd = *out;
         float *f;
+        if (k >= 3) SCN_CUDA(cudaStreamWaitEvent(up, m->ev_k[slot], 0)); // the kernel of chunk k-3 has read this slot's inputs
 #define IN_F(field) if (in->field) { f = cv.take<float>(c); SCN_CUDA(h2d(f, in->field, b, c, s)); di.field = f; }
 #define IN_U(field) if (in->field) { uint32_t *q = cv.take<uint32_t>(c); SCN_CUDA(h2d(q, in->field, b, c, s)); di.field = q; }
         IN_F(px) IN_F(py) IN_F(pz) IN_F(dx) IN_F(dy) IN_F(dz) IN_F(t) IN_F(info_t) IN_U(pix_x) IN_U(pix_y) IN_U(pix_spp) IN_U(pix_seg)
         for (int i = 0; i < 7; ++i) { di.ctx[i] = nullptr; if (has_ctx) { f = cv.take<float>(c); SCN_CUDA(h2d(f, in->ctx[i], b, c, s)); di.ctx[i] = f; } }
 #undef IN_F
 #undef IN_U
+        SCN_CUDA(cudaEventRecord(m->ev_in[slot], up));
         if (out->val) dd.val = cv.take<float>(c);
         if (out->gx) dd.gx = cv.take<float>(c);
         if (out->gy) dd.gy = cv.take<float>(c);
         if (out->gz) dd.gz = cv.take<float>(c);
         if (out->gp_id) dd.gp_id = cv.take<int32_t>(c);
-        if (int rc = scn_eval_batch(m, &di, &dd, c, what, s)) return rc;
+        SCN_CUDA(cudaStreamWaitEvent(run, m->ev_in[slot], 0));
+        if (k >= 3) SCN_CUDA(cudaStreamWaitEvent(run, m->ev_out[slot], 0)); // chunk k-3's results have left this slot
+        if (int rc = scn_eval_batch(m, &di, &dd, c, what, run)) return rc;
+        SCN_CUDA(cudaEventRecord(m->ev_k[slot], run));
+        SCN_CUDA(cudaStreamWaitEvent(down, m->ev_k[slot], 0));
+        s = down;
         if (out->val) SCN_CUDA(d2h(out->val, b, dd.val, c, s));
         if (out->gx) SCN_CUDA(d2h(out->gx, b, dd.gx, c, s));
         if (out->gy) SCN_CUDA(d2h(out->gy, b, dd.gy, c, s));
         if (out->gz) SCN_CUDA(d2h(out->gz, b, dd.gz, c, s));
         if (out->gp_id) SCN_CUDA(d2h(out->gp_id, b, dd.gp_id, c, s));
+        SCN_CUDA(cudaEventRecord(m->ev_out[slot], down));
     }
     for (int i = 0; i < 3; ++i) SCN_CUDA(cudaStreamSynchronize(m->streams[i]));
     return SCN_OK;
@@ -475,7 +501,7 @@ static int query_host(scn_medium *m, const scn_rays *rays, const scn_state *stat
     if (n == 0) return SCN_OK;
     std::lock_guard<std::mutex> lock(m->mu);
     DeviceGuard g(m->device); if (!g.ok) return set_error(SCN_ECUDA, "cannot select device %d", m->device);
-    size_t chunk = n < HOST_CHUNK ? n : HOST_CHUNK;
+    size_t chunk = host_chunk(n);
     size_t per = ((chunk * 4 + 255) & ~(size_t)255) * 48;
     if (int rc = ensure_arena(m, per)) return rc;
     int slot = 0;
