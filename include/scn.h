@@ -9,7 +9,11 @@
  *     returns the message of the calling thread's last failure.  No exception crosses the ABI.
  *   - batch buffers are caller-owned DEVICE pointers (struct-of-arrays, one element per query);
  *     the *_host variants take HOST pointers and do the host<->device copies themselves, through
- *     a staging arena owned by the medium (grown on first use, reused afterwards).
+ *     a staging arena owned by the medium (grown on first use, reused afterwards).  Host buffers
+ *     SHOULD be page-locked (cudaHostAlloc / cudaHostRegister): pageable buffers give the same
+ *     results, but the driver stages every copy and the upload / kernel / download stages of the
+ *     pipeline no longer overlap (bench.py reports both: e2e.value pinned, e2e.pageable).
+ *   - a wavefront holds at most 2^30 queries (SCN_EINVAL above, before anything is enqueued).
  *   - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream).  Calls on
  *     distinct streams are re-entrant; a scn_medium is immutable after creation.
  *   - optional pointers may be NULL where stated.
@@ -24,7 +28,7 @@
 extern "C" {
 #endif
 
-#define SCN_ABI_VERSION 3
+#define SCN_ABI_VERSION 4
 
 /* error codes */
 #define SCN_OK 0
@@ -232,6 +236,24 @@ int scn_desc_from_json(const char *medium_json, scn_medium_desc *desc);
 int scn_medium_create(const scn_medium_desc *desc, int device, scn_medium **out);
 void scn_medium_destroy(scn_medium *m);
 
+/* Which kernel family serves a medium (no reference counterpart: the reference has one code path).  Configurations outside the
+ * tuned kernels' coverage run on the one-thread-per-ray generic kernels — correct, golden-checked, several times slower — and
+ * this call is how a caller sees that instead of discovering it in a profile. */
+#define SCN_KERNEL_GENERIC 0       /* k_sample_distance / k_transmittance / k_eval_noise: any configuration                     */
+#define SCN_KERNEL_MARCH3D 1       /* k_march: 3D sampling, squared-exponential kernel, shared-memory impulse cache             */
+#define SCN_KERNEL_MARCH1D 2       /* k_cond1d -> k_march1d -> k_finish1d: 1D sampling, register cell window                    */
+#define SCN_KERNEL_FAST_NOISE3D 3  /* k_fast_noise3d: SCN_EVAL_NOISE of stationary 3D media (the roofline kernel)               */
+typedef struct scn_medium_info_t {
+    int32_t query_kernel;          /* SCN_KERNEL_* serving scn_sample_distance_batch / scn_transmittance_batch                  */
+    int32_t eval_kernel;           /* SCN_KERNEL_* serving scn_eval_batch(SCN_EVAL_NOISE)                                        */
+    int32_t march_block;           /* threads per block of the query kernel (0: generic)                                        */
+    int32_t cache_entries;         /* k_march: impulse-cache capacity per lane and level                                        */
+    uint32_t smem_bytes;           /* k_march: dynamic shared memory per block                                                  */
+    int32_t device, sm_count;
+    float kernel_radius;           /* splattingKernelRadius of the sampling space = lattice cell size                           */
+} scn_medium_info_t;
+int scn_medium_info(const scn_medium *m, scn_medium_info_t *out);
+
 /* SparseConvolutionNoiseRealization::evaluateNoise3D / evaluateValue / evaluateGradient */
 int scn_eval_batch(const scn_medium *m, const scn_eval_in *in, const scn_eval_out *out, size_t n, int what, void *stream);
 int scn_eval_batch_host(scn_medium *m, const scn_eval_in *in, const scn_eval_out *out, size_t n, int what);
@@ -263,6 +285,10 @@ int scn_debug_pcg_stream(const uint32_t *seed32, float *out, size_t n, int draws
 /* per-cell impulses exactly as cell3D generates them: out[(i*count + k)*4 + {0,1,2,3}] = x, y, z, w */
 int scn_debug_cell_impulses(const uint32_t *ci, const uint32_t *cj, const uint32_t *ck, uint32_t seed, uint32_t count,
                             float *out, size_t n, void *stream);
+
+/* test hook: on != 0 makes the query entry points of this medium use the generic one-thread-per-ray kernels even where a tuned
+ * kernel covers the configuration (the tests compare the two families on the same wavefront) */
+int scn_debug_force_generic(scn_medium *m, int on);
 
 /* per point: how many of the 27*N impulses generated by evaluateNoise3D pass the rejection test |p - p_i|^2 < 1
  * (math/SparseConvolutionNoise.cpp:389) — stationary 3D media; proves the accepted-impulse SETS match the CPU's. */

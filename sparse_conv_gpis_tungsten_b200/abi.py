@@ -72,6 +72,13 @@ class NeeIn(C.Structure):
                [(k, u32p) for k in ("pix_x", "pix_y", "pix_spp", "pix_seg")] + [("scene_seed", C.c_uint32), ("ctx", f32p * 7)]
 
 
+class MediumInfo(C.Structure):
+    _fields_ = [("query_kernel", C.c_int32), ("eval_kernel", C.c_int32), ("march_block", C.c_int32), ("cache_entries", C.c_int32), ("smem_bytes", C.c_uint32),
+                ("device", C.c_int32), ("sm_count", C.c_int32), ("kernel_radius", C.c_float)]
+
+
+KERNEL_NAMES = {0: "generic", 1: "k_march", 2: "k_march1d", 3: "k_fast_noise3d"}
+
 # every symbol include/scn.h declares: name -> (restype, argtypes)
 MediumP = C.c_void_p
 SYMBOLS = {
@@ -90,6 +97,8 @@ SYMBOLS = {
     "scn_transmittance_batch_host": (C.c_int, [MediumP, C.POINTER(Rays), C.POINTER(State), f32p, C.c_size_t]),
     "scn_nee_pdf_batch": (C.c_int, [MediumP, C.POINTER(NeeIn), f32p, C.c_size_t, C.c_void_p]),
     "scn_nee_grad_batch": (C.c_int, [MediumP, C.POINTER(NeeIn), f32p, f32p, f32p, C.c_size_t, C.c_void_p]),
+    "scn_medium_info": (C.c_int, [MediumP, C.POINTER(MediumInfo)]),
+    "scn_debug_force_generic": (C.c_int, [MediumP, C.c_int]),
     "scn_debug_hash4": (C.c_int, [u32p, u32p, u32p, u32p, u32p, C.c_size_t, C.c_void_p]),
     "scn_debug_pcg_stream": (C.c_int, [u32p, f32p, C.c_size_t, C.c_int, C.c_void_p]),
     "scn_debug_cell_impulses": (C.c_int, [u32p, u32p, u32p, C.c_uint32, C.c_uint32, f32p, C.c_size_t, C.c_void_p]),
@@ -118,7 +127,7 @@ def load():
         fn = getattr(lib, name)  # AttributeError if the symbol is not exported
         fn.restype = res
         fn.argtypes = args
-    if lib.scn_abi_version() != 3:
+    if lib.scn_abi_version() != 4:
         raise ImportError("libscn_b200.so ABI version mismatch")
     _lib = lib
     return lib

@@ -184,6 +184,8 @@ struct scn_medium {
     int sm_count = 0;
     int march_block = 0; // 128 / 64, 0 = generic kernels only
     bool march1d = false; // 1D-sampling media covered by k_march1d (scn_march1d.cuh)
+    cudaMemPool_t pool = nullptr; // k_march1d's per-call scratch (stream-ordered allocations of this medium only)
+    bool force_generic = false;   // scn_debug_force_generic: tests compare the tuned kernels with the one-thread-per-ray ones
 };
 
 static inline unsigned grid_for(size_t n) { return (unsigned)((n + BLOCK - 1) / BLOCK); }
@@ -195,22 +197,16 @@ struct DeviceGuard {
     ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
 };
 
-// cached wavefront march (scn_march.cuh) for the configurations it covers; SCN_FORCE_GENERIC=1 keeps the generic walk
-static bool use_march(const scn_medium *m) {
-    static const bool forced = [] { const char *e = getenv("SCN_FORCE_GENERIC"); return e && e[0] == '1'; }();
-    return (m->march_block != 0 || m->march1d) && !forced;
-}
+// cached wavefront march (scn_march.cuh, scn_march1d.cuh) for the configurations it covers
+static bool use_march(const scn_medium *m) { return (m->march_block != 0 || m->march1d) && !m->force_generic; }
+constexpr size_t MAX_WAVEFRONT = 0x40000000u; // the persistent kernels' ray counter is 32 bits wide
 template <bool TRANSMIT>
 static int launch_march(const scn_medium *m, const Rays &kr, const State &ks, const Samples &ko, float *T, uint32_t *n_evals, size_t n, cudaStream_t s) {
-    for (size_t b = 0; b < n; b += 0x40000000u) { // the ray counter is 32 bits wide
-        unsigned c = (unsigned)(n - b < 0x40000000u ? n - b : 0x40000000u);
-        MarchArgs A; A.r = kr; A.s = ks; A.o = ko; A.T = T; A.n_evals = n_evals; A.n = c; A.K = march_cache_entries(m->P.n_imp, m->P.iso3d != 0);
-        if (b) { return set_error(SCN_EINVAL, "batches above 2^30 rays are not supported"); }
-        A.counter = m->counters + (m->next_counter.fetch_add(1) % scn_medium::COUNTERS);
-        SCN_CUDA(cudaMemsetAsync(A.counter, 0, sizeof(unsigned int), s));
-        cudaError_t e = m->march1d ? launch_march1d_t<TRANSMIT>(m->P, A, m->sm_count, s) : launch_march_t<TRANSMIT>(m->P, A, m->march_block, m->sm_count, s);
-        if (e != cudaSuccess) return cuda_fail(e, m->march1d ? "k_march1d" : "k_march");
-    }
+    MarchArgs A; A.r = kr; A.s = ks; A.o = ko; A.T = T; A.n_evals = n_evals; A.n = (unsigned)n; A.K = march_cache_entries(m->P.n_imp, m->P.iso3d != 0);
+    A.counter = m->counters + (m->next_counter.fetch_add(1) % scn_medium::COUNTERS);
+    SCN_CUDA(cudaMemsetAsync(A.counter, 0, sizeof(unsigned int), s));
+    cudaError_t e = m->march1d ? launch_march1d_t<TRANSMIT>(m->P, A, m->sm_count, m->pool, s) : launch_march_t<TRANSMIT>(m->P, A, m->march_block, m->sm_count, s);
+    if (e != cudaSuccess) return cuda_fail(e, m->march1d ? "k_march1d" : "k_march");
     return SCN_OK;
 }
 
@@ -242,10 +238,13 @@ int scn_medium_create(const scn_medium_desc *desc, int device, scn_medium **out)
         cudaError_t e1 = cudaDeviceGetAttribute(&m->sm_count, cudaDevAttrMultiProcessorCount, device);
         cudaError_t e2 = cudaMalloc((void **)&m->counters, scn_medium::COUNTERS * sizeof(unsigned int));
         if (e1 != cudaSuccess || e2 != cudaSuccess) { delete m; return cuda_fail(e1 != cudaSuccess ? e1 : e2, "scn_medium_create"); }
-        if (m->march1d) { // k_march1d's per-call scratch comes from the stream-ordered pool: keep freed blocks cached instead of returning them at every sync
-            cudaMemPool_t pool; unsigned long long keep = ~0ULL;
-            if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
-            cudaGetLastError();
+        if (m->march1d) { // k_march1d's per-call scratch: a pool of this medium's own that keeps freed blocks cached instead of returning them at every sync
+            cudaMemPoolProps props{}; props.allocType = cudaMemAllocationTypePinned; props.handleTypes = cudaMemHandleTypeNone;
+            props.location.type = cudaMemLocationTypeDevice; props.location.id = device;
+            unsigned long long keep = ~0ULL;
+            cudaError_t e3 = cudaMemPoolCreate(&m->pool, &props);
+            if (e3 == cudaSuccess) e3 = cudaMemPoolSetAttribute(m->pool, cudaMemPoolAttrReleaseThreshold, &keep);
+            if (e3 != cudaSuccess) { if (m->pool) cudaMemPoolDestroy(m->pool); cudaFree(m->counters); delete m; return cuda_fail(e3, "scn_medium_create: memory pool"); }
         }
     }
     *out = m;
@@ -259,6 +258,7 @@ void scn_medium_destroy(scn_medium *m) {
         for (int i = 0; i < 3; ++i) { if (m->arena[i]) cudaFree(m->arena[i]); if (m->streams[i]) cudaStreamDestroy(m->streams[i]);
                                       if (m->ev_in[i]) cudaEventDestroy(m->ev_in[i]); if (m->ev_k[i]) cudaEventDestroy(m->ev_k[i]); if (m->ev_out[i]) cudaEventDestroy(m->ev_out[i]); }
         if (m->counters) cudaFree(m->counters);
+        if (m->pool) { cudaDeviceSynchronize(); cudaMemPoolDestroy(m->pool); }
     }
     delete m;
 }
@@ -325,10 +325,10 @@ int scn_sample_distance_batch(const scn_medium *m, const scn_rays *rays, const s
     if (n == 0) return SCN_OK; // an empty wavefront is a no-op (empty buffers may be NULL)
     if (!out->ok || !out->exited || !out->t || !out->continued_t || !out->gx || !out->gy || !out->gz || !out->gp_id || !out->scheme || !out->weight)
         return set_error(SCN_EINVAL, "samples: every output but n_evals is required");
+    if (n > MAX_WAVEFRONT) return set_error(SCN_EINVAL, "wavefronts above 2^30 rays are not supported (split the batch)"); // before anything is enqueued: the state is updated in place
     Rays kr; State ks;
     if (int rc = to_rays(rays, kr)) return rc;
     if (int rc = to_state(state, ks)) return rc;
-    if (n == 0) return SCN_OK;
     DeviceGuard g(m->device); if (!g.ok) return set_error(SCN_ECUDA, "cannot select device %d", m->device);
     Samples ko; ko.ok = out->ok; ko.exited = out->exited; ko.t = out->t; ko.cont_t = out->continued_t; ko.gx = out->gx; ko.gy = out->gy; ko.gz = out->gz;
     ko.gp_id = out->gp_id; ko.scheme = out->scheme; ko.weight = out->weight; ko.n_evals = out->n_evals;
@@ -338,6 +338,7 @@ int scn_sample_distance_batch(const scn_medium *m, const scn_rays *rays, const s
 }
 
 static int transmittance_impl(const scn_medium *m, const scn_rays *rays, const scn_state *state, float *T, uint32_t *n_evals, size_t n, cudaStream_t s) {
+    if (n > MAX_WAVEFRONT) return set_error(SCN_EINVAL, "wavefronts above 2^30 rays are not supported (split the batch)");
     Rays kr; State ks;
     if (int rc = to_rays(rays, kr)) return rc;
     if (int rc = to_state(state, ks)) return rc;
@@ -375,6 +376,27 @@ int scn_nee_grad_batch(const scn_medium *m, const scn_nee_in *in, float *gx, flo
     return nee_impl(m, in, nullptr, gx, gy, gz, n, stream);
 }
 
+// test hook: serve this medium with the one-thread-per-ray generic kernels even where a tuned kernel covers it
+int scn_debug_force_generic(scn_medium *m, int on) {
+    if (!m) return set_error(SCN_EINVAL, "null argument");
+    m->force_generic = on != 0;
+    return SCN_OK;
+}
+
+int scn_medium_info(const scn_medium *m, scn_medium_info_t *out) {
+    if (!m || !out) return set_error(SCN_EINVAL, "null argument");
+    memset(out, 0, sizeof(*out));
+    const bool tuned = use_march(m);
+    out->query_kernel = !tuned ? SCN_KERNEL_GENERIC : (m->march1d ? SCN_KERNEL_MARCH1D : SCN_KERNEL_MARCH3D);
+    out->eval_kernel = fast_noise3d_supported(m->P) ? SCN_KERNEL_FAST_NOISE3D : SCN_KERNEL_GENERIC;
+    out->march_block = m->march1d ? MARCH1D_BLOCK : m->march_block;
+    out->cache_entries = m->march_block ? march_cache_entries(m->P.n_imp, m->P.iso3d != 0) : 0;
+    out->smem_bytes = m->march_block ? (uint32_t)march_smem_total(m->P, out->cache_entries, m->march_block) : 0;
+    out->device = m->device; out->sm_count = m->sm_count;
+    out->kernel_radius = m->P.iso3d || m->P.sampling_1d ? m->P.R_iso : m->P.R_world;
+    return SCN_OK;
+}
+
 int scn_debug_hash4(const uint32_t *a, const uint32_t *b, const uint32_t *c, const uint32_t *d, uint32_t *out, size_t n, void *stream) {
     if (!a || !b || !c || !d || !out) return set_error(SCN_EINVAL, "null argument");
     if (n == 0) return SCN_OK;
@@ -405,8 +427,11 @@ int scn_debug_accepted_counts(const scn_medium *m, const float *px, const float 
 }
 
 // ---------------------------------------------------------------- host-buffer entry points (the thin Tungsten shim calls these)
-// Chunks of the batch travel host -> device -> kernel -> host on three round-robin streams, so the H2D copy of
-// chunk k+1, the kernel of chunk k and the D2H copy of chunk k-1 overlap.  The arena is grown once and reused.
+// Chunks of the batch travel host -> device -> kernel -> host through a three-slot arena (HostPipe below): the H2D copy of chunk
+// k+1, the kernel of chunk k and the D2H copy of chunk k-1 overlap.  The arena is grown once and reused.
+// The caller's buffers should be page-locked (cudaHostAlloc / cudaHostRegister): with pageable memory every cudaMemcpyAsync is
+// staged by the driver and blocks the calling thread, so the three stages no longer overlap (results are identical, throughput is
+// what bench.py reports as e2e.pageable).
 static int ensure_arena(scn_medium *m, size_t bytes_per_slot) {
     for (int i = 0; i < 3; ++i) if (!m->streams[i]) SCN_CUDA(cudaStreamCreateWithFlags(&m->streams[i], cudaStreamNonBlocking));
     for (int i = 0; i < 3; ++i) if (!m->ev_out[i]) {
@@ -420,11 +445,10 @@ static int ensure_arena(scn_medium *m, size_t bytes_per_slot) {
     m->arena_cap = bytes_per_slot;
     return SCN_OK;
 }
-// Queries per pipeline stage of the *_host entry points: at most 2^22 (SCN_HOST_CHUNK_LOG2 = 16..24 overrides the cap for tuning on a
-// given host), at least 2^16, and small enough that a batch makes eight stages, so that mid-sized batches overlap their copies too.
+// Queries per pipeline stage of the *_host entry points: at most 2^22, at least 2^16, and small enough that a batch makes eight
+// stages, so that mid-sized batches overlap their copies too.
 static size_t host_chunk(size_t n) {
-    const char *e = getenv("SCN_HOST_CHUNK_LOG2"); int l = e ? atoi(e) : 22;
-    const size_t cap = (size_t)1 << (l < 16 ? 16 : (l > 24 ? 24 : l));
+    const size_t cap = (size_t)1 << 22;
     size_t c = ((n + 7) / 8 + 255) & ~(size_t)255;
     if (c < ((size_t)1 << 16)) c = (size_t)1 << 16;
     if (c > cap) c = cap;
@@ -440,6 +464,63 @@ template <typename T> static cudaError_t h2d(T *dst, const T *src, size_t first,
 template <typename T> static cudaError_t d2h(T *dst, size_t first, const T *src, size_t count, cudaStream_t s) { return cudaMemcpyAsync(dst + first, src, count * sizeof(T), cudaMemcpyDeviceToHost, s); }
 extern "C" {
 
+// One stream per stage: every H2D copy on `up`, every kernel on `run`, every D2H copy on `down`, chained by events per arena slot
+// (three slots), so that each copy engine sees its transfers back to back in batch order and the two directions stay busy at once:
+// H2D of chunk k+1 || kernel of chunk k || D2H of chunk k-1.  `body(b, c, slot, up, run, down)` enqueues one chunk in three parts
+// through the three callbacks below.  On any failure every stream is drained before returning, so that no copy into or out of the
+// caller's buffers (or the arena) is still in flight when the caller frees them or retries.
+struct HostPipe {
+    scn_medium *m; cudaStream_t up, run, down; size_t k = 0; int slot = 0;
+    explicit HostPipe(scn_medium *m_) : m(m_), up(m_->streams[0]), run(m_->streams[1]), down(m_->streams[2]) {}
+    int begin_upload() { if (k >= 3) SCN_CUDA(cudaStreamWaitEvent(up, m->ev_k[slot], 0)); return SCN_OK; } // the kernel of chunk k-3 has read this slot's inputs
+    int begin_kernel() {
+        SCN_CUDA(cudaEventRecord(m->ev_in[slot], up)); SCN_CUDA(cudaStreamWaitEvent(run, m->ev_in[slot], 0));
+        if (k >= 3) SCN_CUDA(cudaStreamWaitEvent(run, m->ev_out[slot], 0)); // chunk k-3's results have left this slot
+        return SCN_OK;
+    }
+    int begin_download() { SCN_CUDA(cudaEventRecord(m->ev_k[slot], run)); SCN_CUDA(cudaStreamWaitEvent(down, m->ev_k[slot], 0)); return SCN_OK; }
+    int end_chunk() { SCN_CUDA(cudaEventRecord(m->ev_out[slot], down)); slot = (slot + 1) % 3; ++k; return SCN_OK; }
+    int drain(int rc) { // rc of the loop; secondary errors while draining are ignored
+        cudaError_t first = cudaSuccess;
+        for (int i = 0; i < 3; ++i) { cudaError_t e = cudaStreamSynchronize(m->streams[i]); if (first == cudaSuccess) first = e; }
+        if (rc != SCN_OK) { cudaGetLastError(); return rc; }
+        return first == cudaSuccess ? SCN_OK : cuda_fail(first, "host pipeline");
+    }
+};
+#define SCN_PIPE(x) do { if (int rc_ = (x)) return rc_; } while (0)
+
+static int eval_host_chunks(scn_medium *m, const scn_eval_in *in, const scn_eval_out *out, size_t n, int what, size_t chunk, HostPipe &hp) {
+    bool has_ctx = true; for (int i = 0; i < 7; ++i) has_ctx = has_ctx && in->ctx[i];
+    for (size_t b = 0; b < n; b += chunk) {
+        size_t c = n - b < chunk ? n - b : chunk;
+        Carver cv{m->arena[hp.slot]};
+        scn_eval_in di = *in; scn_eval_out dd = *out;
+        float *f;
+        SCN_PIPE(hp.begin_upload());
+#define IN_F(field) if (in->field) { f = cv.take<float>(c); SCN_CUDA(h2d(f, in->field, b, c, hp.up)); di.field = f; }
+#define IN_U(field) if (in->field) { uint32_t *q = cv.take<uint32_t>(c); SCN_CUDA(h2d(q, in->field, b, c, hp.up)); di.field = q; }
+        IN_F(px) IN_F(py) IN_F(pz) IN_F(dx) IN_F(dy) IN_F(dz) IN_F(t) IN_F(info_t) IN_U(pix_x) IN_U(pix_y) IN_U(pix_spp) IN_U(pix_seg)
+        for (int i = 0; i < 7; ++i) { di.ctx[i] = nullptr; if (has_ctx) { f = cv.take<float>(c); SCN_CUDA(h2d(f, in->ctx[i], b, c, hp.up)); di.ctx[i] = f; } }
+#undef IN_F
+#undef IN_U
+        if (out->val) dd.val = cv.take<float>(c);
+        if (out->gx) dd.gx = cv.take<float>(c);
+        if (out->gy) dd.gy = cv.take<float>(c);
+        if (out->gz) dd.gz = cv.take<float>(c);
+        if (out->gp_id) dd.gp_id = cv.take<int32_t>(c);
+        SCN_PIPE(hp.begin_kernel());
+        SCN_PIPE(scn_eval_batch(m, &di, &dd, c, what, hp.run));
+        SCN_PIPE(hp.begin_download());
+        if (out->val) SCN_CUDA(d2h(out->val, b, dd.val, c, hp.down));
+        if (out->gx) SCN_CUDA(d2h(out->gx, b, dd.gx, c, hp.down));
+        if (out->gy) SCN_CUDA(d2h(out->gy, b, dd.gy, c, hp.down));
+        if (out->gz) SCN_CUDA(d2h(out->gz, b, dd.gz, c, hp.down));
+        if (out->gp_id) SCN_CUDA(d2h(out->gp_id, b, dd.gp_id, c, hp.down));
+        SCN_PIPE(hp.end_chunk());
+    }
+    return SCN_OK;
+}
+
 int scn_eval_batch_host(scn_medium *m, const scn_eval_in *in, const scn_eval_out *out, size_t n, int what) {
     if (!m || !in || !out) return set_error(SCN_EINVAL, "null argument");
     if (n == 0) return SCN_OK;
@@ -449,68 +530,18 @@ int scn_eval_batch_host(scn_medium *m, const scn_eval_in *in, const scn_eval_out
     size_t chunk = host_chunk(n);
     size_t per = ((chunk * 4 + 255) & ~(size_t)255) * 32; // <= 32 arrays of 4-byte elements
     if (int rc = ensure_arena(m, per)) return rc;
-    bool has_ctx = true; for (int i = 0; i < 7; ++i) has_ctx = has_ctx && in->ctx[i];
-    // One stream per stage: every H2D copy on `up`, every kernel on `run`, every D2H copy on `down`, chained by events per arena slot,
-    // so that each copy engine sees its transfers back to back in batch order and the two directions stay busy at once.
-    cudaStream_t up = m->streams[0], run = m->streams[1], down = m->streams[2];
-    int slot = 0; size_t k = 0;
-    for (size_t b = 0; b < n; b += chunk, slot = (slot + 1) % 3, ++k) {
-        size_t c = n - b < chunk ? n - b : chunk;
-        cudaStream_t s = up;
-        Carver cv{m->arena[slot]};
-        scn_eval_in di = *in; scn_eval_out dd = *out;
-        float *f;
-        if (k >= 3) SCN_CUDA(cudaStreamWaitEvent(up, m->ev_k[slot], 0)); // the kernel of chunk k-3 has read this slot's inputs
-#define IN_F(field) if (in->field) { f = cv.take<float>(c); SCN_CUDA(h2d(f, in->field, b, c, s)); di.field = f; }
-#define IN_U(field) if (in->field) { uint32_t *q = cv.take<uint32_t>(c); SCN_CUDA(h2d(q, in->field, b, c, s)); di.field = q; }
-        IN_F(px) IN_F(py) IN_F(pz) IN_F(dx) IN_F(dy) IN_F(dz) IN_F(t) IN_F(info_t) IN_U(pix_x) IN_U(pix_y) IN_U(pix_spp) IN_U(pix_seg)
-        for (int i = 0; i < 7; ++i) { di.ctx[i] = nullptr; if (has_ctx) { f = cv.take<float>(c); SCN_CUDA(h2d(f, in->ctx[i], b, c, s)); di.ctx[i] = f; } }
-#undef IN_F
-#undef IN_U
-        SCN_CUDA(cudaEventRecord(m->ev_in[slot], up));
-        if (out->val) dd.val = cv.take<float>(c);
-        if (out->gx) dd.gx = cv.take<float>(c);
-        if (out->gy) dd.gy = cv.take<float>(c);
-        if (out->gz) dd.gz = cv.take<float>(c);
-        if (out->gp_id) dd.gp_id = cv.take<int32_t>(c);
-        SCN_CUDA(cudaStreamWaitEvent(run, m->ev_in[slot], 0));
-        if (k >= 3) SCN_CUDA(cudaStreamWaitEvent(run, m->ev_out[slot], 0)); // chunk k-3's results have left this slot
-        if (int rc = scn_eval_batch(m, &di, &dd, c, what, run)) return rc;
-        SCN_CUDA(cudaEventRecord(m->ev_k[slot], run));
-        SCN_CUDA(cudaStreamWaitEvent(down, m->ev_k[slot], 0));
-        s = down;
-        if (out->val) SCN_CUDA(d2h(out->val, b, dd.val, c, s));
-        if (out->gx) SCN_CUDA(d2h(out->gx, b, dd.gx, c, s));
-        if (out->gy) SCN_CUDA(d2h(out->gy, b, dd.gy, c, s));
-        if (out->gz) SCN_CUDA(d2h(out->gz, b, dd.gz, c, s));
-        if (out->gp_id) SCN_CUDA(d2h(out->gp_id, b, dd.gp_id, c, s));
-        SCN_CUDA(cudaEventRecord(m->ev_out[slot], down));
-    }
-    for (int i = 0; i < 3; ++i) SCN_CUDA(cudaStreamSynchronize(m->streams[i]));
-    return SCN_OK;
+    HostPipe hp(m);
+    return hp.drain(eval_host_chunks(m, in, out, n, what, chunk, hp));
 }
 
-static int query_host(scn_medium *m, const scn_rays *rays, const scn_state *state, const scn_samples *out, float *T_out, size_t n) {
-    if (!m || !rays || !state) return set_error(SCN_EINVAL, "null argument");
-    if (n == 0) return SCN_OK;
-    Rays kr; State ks;
-    if (int rc = to_rays(rays, kr)) return rc;
-    if (int rc = to_state(state, ks)) return rc;
-    if (out && (!out->ok || !out->exited || !out->t || !out->continued_t || !out->gx || !out->gy || !out->gz || !out->gp_id || !out->scheme || !out->weight))
-        return set_error(SCN_EINVAL, "samples: every output but n_evals is required");
-    if (n == 0) return SCN_OK;
-    std::lock_guard<std::mutex> lock(m->mu);
-    DeviceGuard g(m->device); if (!g.ok) return set_error(SCN_ECUDA, "cannot select device %d", m->device);
-    size_t chunk = host_chunk(n);
-    size_t per = ((chunk * 4 + 255) & ~(size_t)255) * 48;
-    if (int rc = ensure_arena(m, per)) return rc;
-    int slot = 0;
-    for (size_t b = 0; b < n; b += chunk, slot = (slot + 1) % 3) {
+static int query_host_chunks(scn_medium *m, const scn_rays *rays, const scn_state *state, const scn_samples *out, float *T_out, size_t n, size_t chunk, bool has_ctx, HostPipe &hp) {
+    for (size_t b = 0; b < n; b += chunk) {
         size_t c = n - b < chunk ? n - b : chunk;
-        cudaStream_t s = m->streams[slot];
-        Carver cv{m->arena[slot]};
+        Carver cv{m->arena[hp.slot]};
         scn_rays dr = *rays; scn_state ds = *state;
         float *f; uint32_t *q; uint8_t *u8; int32_t *i32;
+        cudaStream_t s = hp.up;
+        SCN_PIPE(hp.begin_upload());
 #define RAY_F(field) f = cv.take<float>(c); SCN_CUDA(h2d(f, rays->field, b, c, s)); dr.field = f;
 #define RAY_U(field) if (rays->field) { q = cv.take<uint32_t>(c); SCN_CUDA(h2d(q, rays->field, b, c, s)); dr.field = q; }
         RAY_F(ox) RAY_F(oy) RAY_F(oz) RAY_F(dx) RAY_F(dy) RAY_F(dz) RAY_F(tmin) RAY_F(tmax) RAY_F(u) RAY_U(px) RAY_U(py) RAY_U(spp) RAY_U(segment)
@@ -523,14 +554,16 @@ static int query_host(scn_medium *m, const scn_rays *rays, const scn_state *stat
         i32 = cv.take<int32_t>(c); SCN_CUDA(h2d(i32, (const int32_t *)state->bounce, b, c, s)); ds.bounce = i32;
         i32 = cv.take<int32_t>(c); SCN_CUDA(h2d(i32, (const int32_t *)state->last_gp_id, b, c, s)); ds.last_gp_id = i32;
         ds.scheme = state->scheme ? cv.take<uint8_t>(c) : nullptr;
-        bool has_ctx = ks.ctx[0] != nullptr;
         for (int i = 0; i < 7; ++i) ds.ctx[i] = has_ctx ? cv.take<float>(c) : nullptr;
         if (out) {
             scn_samples dd = *out;
             dd.ok = cv.take<uint8_t>(c); dd.exited = cv.take<uint8_t>(c); dd.t = cv.take<float>(c); dd.continued_t = cv.take<float>(c);
             dd.gx = cv.take<float>(c); dd.gy = cv.take<float>(c); dd.gz = cv.take<float>(c); dd.gp_id = cv.take<int32_t>(c); dd.scheme = cv.take<uint8_t>(c);
             dd.weight = cv.take<float>(c); dd.n_evals = out->n_evals ? cv.take<uint32_t>(c) : nullptr;
-            if (int rc = scn_sample_distance_batch(m, &dr, &ds, &dd, c, s)) return rc;
+            SCN_PIPE(hp.begin_kernel());
+            SCN_PIPE(scn_sample_distance_batch(m, &dr, &ds, &dd, c, hp.run));
+            SCN_PIPE(hp.begin_download());
+            s = hp.down;
             SCN_CUDA(d2h(out->ok, b, dd.ok, c, s)); SCN_CUDA(d2h(out->exited, b, dd.exited, c, s)); SCN_CUDA(d2h(out->t, b, dd.t, c, s));
             SCN_CUDA(d2h(out->continued_t, b, dd.continued_t, c, s)); SCN_CUDA(d2h(out->gx, b, dd.gx, c, s)); SCN_CUDA(d2h(out->gy, b, dd.gy, c, s));
             SCN_CUDA(d2h(out->gz, b, dd.gz, c, s)); SCN_CUDA(d2h(out->gp_id, b, dd.gp_id, c, s)); SCN_CUDA(d2h(out->scheme, b, dd.scheme, c, s));
@@ -543,12 +576,31 @@ static int query_host(scn_medium *m, const scn_rays *rays, const scn_state *stat
             if (has_ctx) for (int i = 0; i < 7; ++i) SCN_CUDA(d2h(state->ctx[i], b, ds.ctx[i], c, s));
         } else {
             float *T = cv.take<float>(c);
-            if (int rc = transmittance_impl(m, &dr, &ds, T, nullptr, c, s)) return rc;
-            SCN_CUDA(d2h(T_out, b, T, c, s));
+            SCN_PIPE(hp.begin_kernel());
+            SCN_PIPE(transmittance_impl(m, &dr, &ds, T, nullptr, c, hp.run));
+            SCN_PIPE(hp.begin_download());
+            SCN_CUDA(d2h(T_out, b, T, c, hp.down));
         }
+        SCN_PIPE(hp.end_chunk());
     }
-    for (int i = 0; i < 3; ++i) SCN_CUDA(cudaStreamSynchronize(m->streams[i]));
     return SCN_OK;
+}
+
+static int query_host(scn_medium *m, const scn_rays *rays, const scn_state *state, const scn_samples *out, float *T_out, size_t n) {
+    if (!m || !rays || !state) return set_error(SCN_EINVAL, "null argument");
+    if (n == 0) return SCN_OK;
+    Rays kr; State ks;
+    if (int rc = to_rays(rays, kr)) return rc;
+    if (int rc = to_state(state, ks)) return rc;
+    if (out && (!out->ok || !out->exited || !out->t || !out->continued_t || !out->gx || !out->gy || !out->gz || !out->gp_id || !out->scheme || !out->weight))
+        return set_error(SCN_EINVAL, "samples: every output but n_evals is required");
+    std::lock_guard<std::mutex> lock(m->mu);
+    DeviceGuard g(m->device); if (!g.ok) return set_error(SCN_ECUDA, "cannot select device %d", m->device);
+    size_t chunk = host_chunk(n);
+    size_t per = ((chunk * 4 + 255) & ~(size_t)255) * 48;
+    if (int rc = ensure_arena(m, per)) return rc;
+    HostPipe hp(m);
+    return hp.drain(query_host_chunks(m, rays, state, out, T_out, n, chunk, ks.ctx[0] != nullptr, hp));
 }
 int scn_sample_distance_batch_host(scn_medium *m, const scn_rays *rays, const scn_state *state, const scn_samples *out, size_t n) {
     if (!out) return set_error(SCN_EINVAL, "null argument");

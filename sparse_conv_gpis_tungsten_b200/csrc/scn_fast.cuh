@@ -197,13 +197,11 @@ __global__ void __launch_bounds__(FAST_BLOCK) k_fast_noise3d(const __grid_consta
 inline void launch_fast_noise3d(const Params &P, const float *px, const float *py, const float *pz, const float *dx, const float *dy, const float *dz,
                                 uint32_t seed, float *oval, float *ogx, float *ogy, float *ogz, size_t n, cudaStream_t s) {
     unsigned grid = (unsigned)((n + FAST_BLOCK - 1) / FAST_BLOCK);
-    static const bool big = !getenv("SCN_FAST_NO_BIG_UNROLL"); // experiment switch: unrolled jump-ahead bodies for N = 8, 16, 32
     const uint64_t inc = 1ULL; // the PCG32 stream increment (_sequence | 1, sampling/UniformSampler.hpp:17-27)
 #define SCN_FAST_LAUNCH(ISO_, N_) k_fast_noise3d<ISO_, N_><<<grid, FAST_BLOCK, 0, s>>>(P, px, py, pz, dx, dy, dz, seed, inc, oval, ogx, ogy, ogz, n)
 #define SCN_FAST_BY_N(ISO_) switch (P.n_imp) { case 1: SCN_FAST_LAUNCH(ISO_, 1); break; case 2: SCN_FAST_LAUNCH(ISO_, 2); break; case 3: SCN_FAST_LAUNCH(ISO_, 3); break; \
-                                               case 4: SCN_FAST_LAUNCH(ISO_, 4); break; case 8: if (big) SCN_FAST_LAUNCH(ISO_, 8); else SCN_FAST_LAUNCH(ISO_, 0); break; \
-                                               case 16: if (big) SCN_FAST_LAUNCH(ISO_, 16); else SCN_FAST_LAUNCH(ISO_, 0); break; \
-                                               case 32: if (big) SCN_FAST_LAUNCH(ISO_, 32); else SCN_FAST_LAUNCH(ISO_, 0); break; default: SCN_FAST_LAUNCH(ISO_, 0); }
+                                               case 4: SCN_FAST_LAUNCH(ISO_, 4); break; case 8: SCN_FAST_LAUNCH(ISO_, 8); break; \
+                                               case 16: SCN_FAST_LAUNCH(ISO_, 16); break; case 32: SCN_FAST_LAUNCH(ISO_, 32); break; default: SCN_FAST_LAUNCH(ISO_, 0); }
     if (P.iso3d) { SCN_FAST_BY_N(true) } else { SCN_FAST_BY_N(false) }
 #undef SCN_FAST_BY_N
 #undef SCN_FAST_LAUNCH

@@ -284,7 +284,8 @@ int desc_from_json(const char *text, scn_medium_desc *d) {
     if (p.i != p.n) return set_error(SCN_EJSON, "JSON parse error: trailing characters at offset %zu", p.i);
     if (root.kind != JVal::Obj) return set_error(SCN_EJSON, "medium JSON must be an object");
     std::string type;
-    if (getS(root, "type", type) && type != "sparse_conv_noise")
+    // "sparse_conv_noise_gpu" is the factory string the Tungsten-side shim registers (oracle/gpu_medium_shim.cpp)
+    if (getS(root, "type", type) && type != "sparse_conv_noise" && type != "sparse_conv_noise_gpu")
         return set_error(SCN_EJSON, "medium type '%s' is not \"sparse_conv_noise\"", type.c_str());
 
     getI(root, "max_bounces", d->max_bounces);

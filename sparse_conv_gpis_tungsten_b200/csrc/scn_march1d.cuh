@@ -130,14 +130,16 @@ struct Scratch1D {
     float *c[7];          // conditioning coefficients (value_scale, gradient_scale, ray_origin); null when the medium never conditions
     float *t_hi, *t_lo;   // crossing / exit distance (double split into two floats)
     float *last_val;
-    uint32_t *flags;      // bit 0: hit, bit 1: nothing left to do (refused / trivial exit), bits 8-15: scheme at the hit, bits 16-31: gp id at the hit
+    uint32_t *flags;      // bit 0: hit, bit 1: nothing left to do (refused / trivial exit), bits 8-15: scheme at the hit
     uint32_t *evals;
+    int32_t *gp_id;       // gp id at the hit: the full int32 of the JSON "id", as the generic and 3D kernels carry it
 };
-constexpr size_t SCRATCH1D_BYTES_PER_RAY = 12 * sizeof(float);
+constexpr size_t SCRATCH1D_BYTES_PER_RAY = 13 * sizeof(float);
 inline Scratch1D scratch1d_carve(void *base, size_t n) {
     Scratch1D X; float *f = (float *)base;
     for (int j = 0; j < 7; ++j) X.c[j] = f + (size_t)j * n;
     X.t_hi = f + 7 * n; X.t_lo = f + 8 * n; X.last_val = f + 9 * n; X.flags = (uint32_t *)(f + 10 * n); X.evals = (uint32_t *)(f + 11 * n);
+    X.gp_id = (int32_t *)(f + 12 * n);
     return X;
 }
 
@@ -338,7 +340,7 @@ __global__ void __launch_bounds__(MARCH1D_BLOCK) k_march1d(const __grid_constant
                 if (hit) scheme = cov_amplitude(P, ray_at(o, rd, t_fin)) < 1e-6f ? SCN_SCHEME_UNI : (uint32_t)P.scheme; // samplingScheme (SCN:51-58)
                 const float th = (float)t_fin;
                 X.t_hi[ri] = th; X.t_lo[ri] = (float)(t_fin - (double)th); X.last_val[ri] = last_val;
-                X.flags[ri] = (hit ? 1u : 0u) | (scheme << 8) | ((uint32_t)gp_id << 16);
+                X.flags[ri] = (hit ? 1u : 0u) | (scheme << 8); X.gp_id[ri] = gp_id;
                 X.evals[ri] = evals;
             }
             phase = PH_FETCH;
@@ -360,7 +362,7 @@ __global__ void __launch_bounds__(MARCH1D_BLOCK) k_finish1d(const __grid_constan
     Coeff c; c.vs = 0.f; c.gs = F3(0, 0, 0); c.org = F3(0, 0, 0);
     if (P.activate_conditioning && !A.s.first_scatter[ri]) { c.vs = X.c[0][ri]; c.gs = F3(X.c[1][ri], X.c[2][ri], X.c[3][ri]); c.org = F3(X.c[4][ri], X.c[5][ri], X.c[6][ri]); }
     Finish F; F.hit = (fl & 1u) != 0u; F.grad_valid = false; F.t = (double)X.t_hi[ri] + (double)X.t_lo[ri]; F.grad = F3(0, 0, 0); F.last_val = X.last_val[ri];
-    F.gp_id_hit = (int)(fl >> 16); F.scheme_hit = (int)((fl >> 8) & 0xffu); F.evals = X.evals[ri];
+    F.gp_id_hit = X.gp_id[ri]; F.scheme_hit = (int)((fl >> 8) & 0xffu); F.evals = X.evals[ri];
     if (F.hit || !P.absorption_only) {
         const Info info = load_info1d(A.r, A.s, ri);
         const uint32_t seed = compute_seed(P, info);
@@ -374,11 +376,12 @@ __global__ void __launch_bounds__(MARCH1D_BLOCK) k_finish1d(const __grid_constan
     finish_ray<false>(P, A, ri, dir, far_t, c, F);
 }
 
-// scratch: stream-ordered allocation on the caller's stream (no synchronisation; concurrent streams get distinct buffers)
+// scratch: stream-ordered allocation on the caller's stream (no synchronisation; concurrent streams get distinct buffers) out of
+// the MEDIUM's own memory pool — the device's default pool, which belongs to the host application, is never touched
 template <bool TRANSMIT>
-inline cudaError_t launch_march1d_t(const Params &P, const MarchArgs &A, int sm_count, cudaStream_t s) {
+inline cudaError_t launch_march1d_t(const Params &P, const MarchArgs &A, int sm_count, cudaMemPool_t pool, cudaStream_t s) {
     void *scratch = nullptr;
-    cudaError_t e = cudaMallocAsync(&scratch, SCRATCH1D_BYTES_PER_RAY * (size_t)A.n, s);
+    cudaError_t e = cudaMallocFromPoolAsync(&scratch, SCRATCH1D_BYTES_PER_RAY * (size_t)A.n, pool, s);
     if (e != cudaSuccess) return e;
     const Scratch1D X = scratch1d_carve(scratch, A.n);
     const unsigned per_ray_grid = (A.n + MARCH1D_BLOCK - 1) / MARCH1D_BLOCK;

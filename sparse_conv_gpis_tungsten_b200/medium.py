@@ -157,6 +157,18 @@ class SparseConvolutionNoiseMedium:
     def from_json(cls, medium_json, device=0):
         return cls(cls.desc_from_json(medium_json), device)
 
+    def info(self):
+        """scn_medium_info: which kernel family serves this medium ("k_march", "k_march1d", "generic"; "k_fast_noise3d" for the noise
+        evaluation), block size, cache capacity, shared memory per block, lattice cell size."""
+        i = abi.MediumInfo()
+        abi.check(self._lib.scn_medium_info(self._h, C.byref(i)))
+        return {"query_kernel": abi.KERNEL_NAMES[i.query_kernel], "eval_kernel": abi.KERNEL_NAMES[i.eval_kernel], "march_block": i.march_block,
+                "cache_entries": i.cache_entries, "smem_bytes": i.smem_bytes, "device": i.device, "sm_count": i.sm_count, "kernel_radius": i.kernel_radius}
+
+    def force_generic(self, on=True):
+        """Test hook (scn_debug_force_generic): serve the queries of this medium with the generic one-thread-per-ray kernels."""
+        abi.check(self._lib.scn_debug_force_generic(self._h, int(bool(on))))
+
     def close(self):
         if getattr(self, "_h", None):
             self._lib.scn_medium_destroy(self._h)

@@ -458,3 +458,117 @@ class GpuImpl:
         pdf = self.m.nee_pdf(self._f(d), self._f(normal), self._f(p), self._f(t_segment)[0], **kw)
         g = self.m.nee_grad(self._f(d), self._f(normal), self._f(p), **kw)
         return self._np(pdf), np.stack([self._np(x) for x in g], 1)
+
+
+# ------------------------------------------------------------------------------------------------ the reference's own renderer
+def ref_render(scene_json, seed=0xBA5EBA11, threads=None, gpu_medium=False, device=0):
+    """Render `scene_json` with the UNMODIFIED reference integrator (oracle/ref_harness.cpp: ref_render) -> ([h, w, 3] float32, seconds).
+    gpu_medium=True registers GpuSparseConvolutionNoiseMedium (oracle/gpu_medium_shim.cpp) and switches every
+    "sparse_conv_noise" medium of the scene to "sparse_conv_noise_gpu": the same integrator, sampler and seed, with
+    Medium::sampleDistance / transmittance served by libscn_b200.so."""
+    import json
+    import tempfile
+    from sparse_conv_gpis_tungsten_b200 import abi
+    L = C.CDLL(REF_LIB)
+    L.ref_last_error.restype = C.c_char_p
+    sc = copy.deepcopy(scene_json)
+    if gpu_medium:
+        L.ref_gpu_medium_last_error.restype = C.c_char_p
+        if L.ref_gpu_medium_register(abi.LIB_PATH.encode(), C.c_int(device)) != 0:
+            raise RuntimeError(L.ref_gpu_medium_last_error().decode())
+        for m in sc["media"]:
+            if m.get("type") == "sparse_conv_noise":
+                m["type"] = "sparse_conv_noise_gpu"
+    res = sc["camera"]["resolution"]
+    w0, h0 = (res, res) if np.isscalar(res) else res
+    rgb = np.zeros((h0, w0, 3), np.float32)
+    with tempfile.TemporaryDirectory() as td:
+        path = os.path.join(td, "scene.json")
+        with open(path, "w") as f:
+            json.dump(sc, f)
+        w, h, sec = C.c_int(), C.c_int(), C.c_double()
+        rc = L.ref_render(path.encode(), int(threads or os.cpu_count() or 1), C.c_uint32(seed), C.byref(w), C.byref(h), rgb.ctypes.data_as(C.c_void_p),
+                          C.c_size_t(rgb.size), C.byref(sec))
+    if rc != 0:
+        raise RuntimeError(L.ref_last_error().decode())
+    return rgb, sec.value
+
+
+def ref_gpu_medium_stats(reset=False):
+    """(sampleDistance calls, transmittance calls, media prepared) served by libscn_b200.so through the shim."""
+    L = C.CDLL(REF_LIB)
+    out = (C.c_ulonglong * 3)()
+    L.ref_gpu_medium_stats(out, C.c_int(int(reset)))
+    return tuple(int(v) for v in out)
+
+
+# ------------------------------------------------------------------------------------------------ large-sample query parity
+PARITY_MEDIA = ["c1_sphere_3d_none", "c3_1d_renewal", "c4_1d_renewalplus_xy_mis", "c5_multires_nonstat_renewalplus", "iso_3d_renewalplus_aniso",
+                "world_3d_renewalplus", "multires_world", "nonstat_bruteforce_iso", "nonstat_bruteforce_world_var", "nonstat_bruteforce_1d_renewalplus",
+                "multires_1d_xy", "multires_1d_renewal"]
+
+
+def checker(medium_json):
+    """The CPU side of a parity test: the compiled UNMODIFIED reference (oracle/_ref) whenever it is present — it travels to the
+    GPU box — and the C restatement (pinned bit for bit against it, tests/test_oracle.py) only where it is not."""
+    return CpuImpl("ref" if have_ref() else "orc", medium_json)
+
+
+def _q(x, q):
+    return float(np.quantile(x, q)) if len(x) else 0.0
+
+
+def query_parity_rates(a, b, Ta=None, Tb=None, step=0.01):
+    """Mismatch RATES of two sampleDistance result sets over the same rays (a = under test, b = checker), SURVEY H-sign taxonomy:
+      decision     ok / exited differ, or the hit lies more than one march step away
+      step_moved   same decision, hit distance off by more than 1e-4 relative (floor 1e-3) but within one march step: a sign that
+                   flipped at one test point of the secant refinement (|f| ~ 1e-9) changes the number of 0.9-shrinks
+      matched      everything else: max / 99.9 % relative error of t, of the gradient (floor: rms of the checker's gradients) and of
+                   each of the 7 conditioning coefficients (floor: rms of that coefficient)"""
+    n = len(a["ok"])
+    dt = np.abs(a["t"].astype(np.float64) - b["t"].astype(np.float64))
+    same = (a["ok"] == b["ok"]) & (a["exited"] == b["exited"])
+    far = dt > np.maximum(step * 1.01, 1e-3 * np.maximum(1.0, np.abs(b["t"])))
+    decision = ~same | (same & (a["ok"] != 0) & far)
+    live = same & ~far & (a["ok"] != 0)
+    t_rel = dt / np.maximum(np.abs(b["t"]), 1e-3)
+    moved = live & (t_rel > 1e-4)
+    m = live & ~moved
+    rep = {"n": n, "decision": int(decision.sum()), "step_moved": int(moved.sum()), "matched": int(m.sum()),
+           "ok_fraction": float((b["ok"] != 0).mean()), "hit_fraction": float(((b["ok"] != 0) & (b["exited"] == 0)).mean()),
+           "t_rel_max": float(t_rel[m].max()) if m.any() else 0.0, "t_rel_p999": _q(t_rel[m], 0.999),
+           "t_abs_max_moved": float(dt[moved].max()) if moved.any() else 0.0}
+    g_floor = max(float(np.sqrt(np.mean(np.asarray(b["grad"][m], np.float64) ** 2))) if m.any() else 1.0, 1e-12)
+    ge = rel_err(a["grad"][m], b["grad"][m], g_floor).max(axis=1) if m.any() else np.zeros(0)
+    rep["grad_rel_max"] = float(ge.max()) if len(ge) else 0.0
+    rep["grad_rel_p999"] = _q(ge, 0.999)
+    cmax, cp = [], []
+    for k in range(7):
+        ca, cb = a["coeffs"][m, k].astype(np.float64), b["coeffs"][m, k].astype(np.float64)
+        fl = max(float(np.sqrt(np.mean(cb * cb))) if len(cb) else 0.0, 1e-6)
+        e = np.abs(ca - cb) / np.maximum(np.abs(cb), fl)
+        cmax.append(float(e.max()) if len(e) else 0.0); cp.append(_q(e, 0.999))
+    rep["ctx_rel_max"] = cmax
+    rep["ctx_rel_p999"] = cp
+    st_a, st_b = a["state"], b["state"]
+    rep["state_int_mismatch"] = int(((st_a["bounce"] != st_b["bounce"]) | (st_a["last_gp_id"] != st_b["last_gp_id"]) |
+                                     (st_a["first_scatter"] != st_b["first_scatter"]))[~decision].sum())
+    rep["scheme_mismatch"] = int((a["scheme"] != b["scheme"])[m].sum())
+    if Ta is not None:
+        rep["transmittance_mismatch"] = int((Ta != Tb).sum())
+    return rep
+
+
+def query_parity_case(name, secondary, n=8192, seed=23, scene_seed=9, impl=None):
+    """One (medium, wavefront) case of the large-sample parity: the library (or `impl`) against the checker."""
+    mj = MEDIA[name]
+    rays, st = camera_rays(n, seed=seed, secondary=secondary)
+    a_impl, b_impl = impl or GpuImpl(mj), checker(mj)
+    a, b = a_impl.sample_distance(rays, st, scene_seed), b_impl.sample_distance(rays, st, scene_seed)
+    rep = query_parity_rates(a, b, a_impl.transmittance(rays, st, scene_seed), b_impl.transmittance(rays, st, scene_seed),
+                             step=float(mj.get("step_size", 0.01)))
+    rep.update(medium=name, wavefront="secondary" if secondary else "primary", checker=b_impl.kind)
+    if impl is None:
+        a_impl.close()
+    b_impl.close()
+    return rep

@@ -18,7 +18,7 @@ def test_header_symbols_exported(built_library):
     assert declared == set(abi.SYMBOLS), declared ^ set(abi.SYMBOLS)
     for name in declared:
         assert hasattr(built_library, name)
-    assert built_library.scn_abi_version() == 3
+    assert built_library.scn_abi_version() == 4
 
 
 def test_desc_layout_and_defaults(built_library):

@@ -80,6 +80,21 @@ def test_oracle_vs_live_reference(name):
         assert np.array_equal(orc_.transmittance(rays, st, 3), ref.transmittance(rays, st, 3))
 
 
+@pytest.mark.skipif(not S.have_ref(), reason="oracle/_ref is only built where /root/reference is mounted")
+@pytest.mark.parametrize("name", S.PARITY_MEDIA)
+def test_oracle_equals_reference_on_the_8k_parity_wavefronts(name):
+    """The restatement equals the compiled reference BIT FOR BIT on the very 8192-ray wavefronts the GPU parity test uses
+    (tests/test_gpu_parity.py::test_march_kernels_vs_reference_8k_rays): every decision, hit distance, gradient, the seven conditioning
+    coefficients, the advanced state and the transmittance.  So a box without oracle/_ref that falls back to the restatement checks
+    against the same numbers."""
+    for secondary in (False, True):
+        r = S.query_parity_case(name, secondary, impl=S.CpuImpl("orc", S.MEDIA[name]))
+        assert r["checker"] == "ref"
+        assert r["decision"] == 0 and r["step_moved"] == 0 and r["transmittance_mismatch"] == 0 and r["state_int_mismatch"] == 0 and r["scheme_mismatch"] == 0, r
+        assert r["t_rel_max"] == 0 and r["grad_rel_max"] == 0 and max(r["ctx_rel_max"]) == 0, r
+        assert r["matched"] > 0.2 * r["n"], r
+
+
 def test_conditioning_residual_invariant():
     """The reference's own run-time self-check (SCN.cpp:469-474,511-515): after conditioning, the realization
     reproduces the target value (and gradient for Renewal+) at the ray origin to < 1e-2."""

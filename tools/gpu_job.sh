@@ -1,18 +1,41 @@
-# one GPU-box visit: parity tests, bench (with and without the big unrolls), ncu launch list, ncu full captures
-set -x; mkdir -p gpurun_out; T=${TAG:-v6}
-nvidia-smi --query-gpu=name,clocks.max.sm --format=csv,noheader; nproc
-python -m pytest tests -m gpu -q -x 2>&1 | tail -5 > gpurun_out/pytest_$T.log; cat gpurun_out/pytest_$T.log
-python bench.py > gpurun_out/bench_$T.json 2> gpurun_out/bench_$T.err || tail -20 gpurun_out/bench_$T.err
-SCN_FAST_NO_BIG_UNROLL=1 python bench.py --steps 3 > gpurun_out/bench_${T}_nobig.json 2> gpurun_out/bench_${T}_nobig.err
-python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/bench_${T}_reference.json 2>/dev/null
-python - <<PY
-import json
-for v in ("$T", "${T}_nobig"):
-    d=json.loads([l for l in open('gpurun_out/bench_%s.json'%v) if l.startswith('{')][-1])
-    print(v, round(d['value']/1e9,3), 'e2e', round(d['e2e']['value']/1e9,3), {k:round(x['evals_per_s']/1e9,3) for k,x in d['extra']['sweep'].items()}, d['extra']['parity_vs_cpu_max_rel_err'], d['extra'].get('medium_queries',{}).get('queries_per_s'), d['extra'].get('medium_queries_c5',{}).get('queries_per_s'))
-PY
-ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches_$T.csv python bench.py --steps 2 --warmup 3 --e2e-points 4194304 > gpurun_out/ncu_launches_$T.log 2>&1
-ncu --set full --clock-control none --import-source on -k regex:k_fast_noise3d --launch-skip 3 -c 1 -f -o gpurun_out/fast_$T python bench.py --steps 1 --warmup 3 --no-extras --e2e-points 1048576 > gpurun_out/ncu_fast_$T.log 2>&1
-ncu --set full --clock-control none --import-source on -k regex:k_march --launch-skip 1 -c 1 -f -o gpurun_out/march_c1_$T python tools/run_queries.py c1_sphere_3d_none 20 1 > gpurun_out/ncu_march_c1_$T.log 2>&1
-ncu --set full --clock-control none --import-source on -k regex:k_march --launch-skip 1 -c 1 -f -o gpurun_out/march_c5_$T python tools/run_queries.py c5_multires_nonstat_renewalplus 20 1 > gpurun_out/ncu_march_c5_$T.log 2>&1
-ls -la gpurun_out
+#!/bin/bash
+# The one GPU job script (run under gpurun):   bash tools/gpu_job.sh <stage> [<stage> ...]      TAG=<suffix of the output files>
+#   tests      pytest -m gpu + smoke()
+#   bench      bench.py (both arms) at N=1
+#   queries    queries/s of the BASELINE media (tools/run_queries.py)
+#   launches   ncu launch list of the bench command (gpu__time_duration.sum)
+#   ncu_fast | ncu_c1 | ncu_c5 | ncu_c3     one `ncu --set full` capture of that kernel
+#   sanitize   compute-sanitizer memcheck / racecheck / initcheck over tools/sanitize_workload.py
+# Everything is written under gpurun_out/ (scratch); what is to be judged is copied into profiles/ afterwards.
+set -x; mkdir -p gpurun_out; T=${TAG:-r02}
+NCU="ncu --set full --clock-control none --import-source on"
+for stage in "$@"; do case $stage in
+tests)
+  python -m pytest tests -m gpu -q -x 2>&1 | tail -15 > gpurun_out/pytest_$T.log; cat gpurun_out/pytest_$T.log
+  python -c "import __graft_entry__ as g; g.smoke()" 2>&1 | tail -2 ;;
+bench)
+  python bench.py > gpurun_out/bench_$T.json 2> gpurun_out/bench_$T.err || tail -20 gpurun_out/bench_$T.err
+  python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/bench_${T}_reference.json 2>/dev/null
+  tail -c 3000 gpurun_out/bench_$T.json ;;
+queries)
+  for name in c1_sphere_3d_none c5_multires_nonstat_renewalplus c3_1d_renewal c4_1d_renewalplus_xy_mis; do
+    python tools/run_queries.py $name 20 3 | tail -2; python tools/run_queries.py $name 20 3 secondary | tail -2
+  done 2>&1 | tee gpurun_out/queries_$T.log ;;
+launches)
+  ncu --metrics gpu__time_duration.sum --clock-control none -c 900 --csv --log-file gpurun_out/launches_$T.csv python bench.py --steps 2 --warmup 3 --e2e-points 4194304 > gpurun_out/ncu_launches_$T.log 2>&1 ;;
+ncu_fast)
+  $NCU -k regex:k_fast_noise3d --launch-skip 2 -c 1 -f -o gpurun_out/fast_$T python bench.py --steps 2 --warmup 3 --no-extras --e2e-points 4194304 > gpurun_out/ncu_fast_$T.log 2>&1 ;;
+ncu_c1)
+  $NCU -k regex:k_march --launch-skip 1 -c 1 -f -o gpurun_out/march_c1_$T python tools/run_queries.py c1_sphere_3d_none 20 1 > gpurun_out/ncu_march_c1_$T.log 2>&1 ;;
+ncu_c5)
+  $NCU -k regex:k_march --launch-skip 1 -c 1 -f -o gpurun_out/march_c5_$T python tools/run_queries.py c5_multires_nonstat_renewalplus 20 1 > gpurun_out/ncu_march_c5_$T.log 2>&1 ;;
+ncu_c3)
+  $NCU -k regex:k_march1d --launch-skip 1 -c 1 -f -o gpurun_out/march1d_$T python tools/run_queries.py c3_1d_renewal 20 1 > gpurun_out/ncu_march1d_$T.log 2>&1 ;;
+sanitize)
+  for tool in memcheck racecheck initcheck; do
+    timeout 900 compute-sanitizer --tool $tool --print-limit 20 python tools/sanitize_workload.py 13 > gpurun_out/sanitize_${tool}_$T.log 2>&1
+    tail -4 gpurun_out/sanitize_${tool}_$T.log
+  done ;;
+*) echo "unknown stage $stage" ;;
+esac; done
+ls -la gpurun_out | tail -8
