@@ -121,6 +121,16 @@ int scn_wf_nee_gather(const scn_wf_paths *paths, const scn_wf_shadow *light_rays
  * wavefront: a sample with a NaN, an infinite component or a component above 65536 becomes black.  Call before scn_wf_accumulate. */
 int scn_wf_clamp_samples(const scn_wf_paths *paths, size_t n, void *stream);
 
+/* The whole render loop of one GPU's tiles in ONE call: for every chunk of spp_chunk samples per pixel
+ *   raygen -> max_bounces x { scn_sample_distance_batch, [nee: setup + two scn_transmittance_batch], shade (+ gather) } -> clamp -> accumulate
+ * enqueued on `stream` without a host synchronisation.  Replaces PathTraceIntegrator::renderTile
+ * (integrators/path_tracer/PathTraceIntegrator.cpp:135-163) over PathTracer::traceSample (PathTracer.cpp:62-169).  The per-path
+ * buffers must hold tile_count * 256 * spp_chunk paths; framebuffer[0] (red or grey) and, with scene.nee, [1] / [2] (green, blue)
+ * hold tile_count * 256 running sums.  light_rays / phase_rays may be NULL when scene.nee == 0. */
+int scn_wf_render(const scn_wf_scene *scene, const scn_medium *m, uint32_t tile_first, uint32_t tile_stride, uint32_t tile_count, uint32_t spp_first,
+                  uint32_t spp_count, uint32_t spp_chunk, const scn_wf_paths *paths, const scn_wf_shadow *light_rays, const scn_wf_shadow *phase_rays,
+                  float *const framebuffer[3], void *stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -340,9 +340,18 @@ __global__ void __launch_bounds__(WF_BLOCK) k_wf_nee_gather(const WfPaths W, con
 
 // k_wf_shade with the reference's bookkeeping of direct emitter hits: an emitter met by the path itself counts only while the path
 // has not scattered (TraceBase.cpp:592-596, 629-637 with wasSpecular = false after handleVolume); RGB throughput.
-__global__ void __launch_bounds__(WF_BLOCK) k_wf_shade_nee(const scn_wf_scene S, const WfPaths W, int32_t bounce, size_t n) {
+// GATHER: k_wf_nee_gather folded in (scn_wf_render): the shadow rays of this bounce were written for live paths only, so the
+// gather of a dead path would add 0 and is skipped with it.
+template <bool GATHER>
+__global__ void __launch_bounds__(WF_BLOCK) k_wf_shade_nee(const scn_wf_scene S, const WfPaths W, const WfShadow L, const WfShadow Q, int32_t bounce, size_t n) {
     const size_t i = (size_t)blockIdx.x * WF_BLOCK + threadIdx.x;
     if (i >= n || !W.alive[i]) return;
+    if (GATHER) {
+        const float tl = L.T[i], tq = Q.T[i];
+        W.radiance[i] += L.contrib[0][i] * tl + Q.contrib[0][i] * tq;
+        W.rad_gb[0][i] += L.contrib[1][i] * tl + Q.contrib[1][i] * tq;
+        W.rad_gb[1][i] += L.contrib[2][i] * tl + Q.contrib[2][i] * tq;
+    }
     if (!W.ok[i]) { wf_finish_rgb(W, i, F3(0, 0, 0)); return; }
     const float wq = W.weight[i];
     f3 thr = F3(W.throughput[i] * wq, W.thr_gb[0][i] * wq, W.thr_gb[1][i] * wq);
@@ -484,7 +493,8 @@ int scn_wf_shade(const scn_wf_scene *scene, const scn_medium *m, const scn_wf_pa
     WfPaths W; if (int rc = wf_paths(paths, W, true)) return rc;
     if (scene->nee) {
         if (int rc = wf_nee_arrays(paths)) return rc;
-        k_wf_shade_nee<<<(unsigned)((n + WF_BLOCK - 1) / WF_BLOCK), WF_BLOCK, 0, (cudaStream_t)stream>>>(*scene, W, bounce, n);
+        WfShadow none{};
+        k_wf_shade_nee<false><<<(unsigned)((n + WF_BLOCK - 1) / WF_BLOCK), WF_BLOCK, 0, (cudaStream_t)stream>>>(*scene, W, none, none, bounce, n);
         return wf_check("k_wf_shade_nee");
     }
     k_wf_shade<<<(unsigned)((n + WF_BLOCK - 1) / WF_BLOCK), WF_BLOCK, 0, (cudaStream_t)stream>>>(*scene, W, bounce, n);
@@ -531,6 +541,52 @@ int scn_wf_accumulate(const float *radiance, float *framebuffer, size_t n_pixels
     if (n_pixels == 0 || spp_count == 0) return SCN_OK;
     k_wf_accumulate<<<(unsigned)((n_pixels + WF_BLOCK - 1) / WF_BLOCK), WF_BLOCK, 0, (cudaStream_t)stream>>>(radiance, framebuffer, n_pixels, spp_count);
     return wf_check("k_wf_accumulate");
+}
+
+// The whole per-rank render loop in one call (what render.py used to drive launch by launch from Python): for every chunk of
+// `spp_chunk` samples per pixel  raygen -> max_bounces x { medium query, [nee setup, two transmittance wavefronts], shade (+ gather) }
+// -> clamp -> accumulate, all enqueued on `stream` with no host synchronisation.  PathTraceIntegrator::renderTile
+// (integrators/path_tracer/PathTraceIntegrator.cpp:135-163) over PathTracer::traceSample (PathTracer.cpp:62-169) for this GPU's tiles.
+int scn_wf_render(const scn_wf_scene *scene, const scn_medium *m, uint32_t tile_first, uint32_t tile_stride, uint32_t tile_count, uint32_t spp_first,
+                  uint32_t spp_count, uint32_t spp_chunk, const scn_wf_paths *paths, const scn_wf_shadow *light_rays, const scn_wf_shadow *phase_rays,
+                  float *const framebuffer[3], void *stream) {
+    if (!scene || !m || !paths || !framebuffer || !framebuffer[0]) return set_error(SCN_EINVAL, "null argument");
+    if (spp_chunk == 0) return set_error(SCN_EINVAL, "render: spp_chunk must be >= 1");
+    const bool nee = scene->nee != 0;
+    if (nee && (!light_rays || !phase_rays || !framebuffer[1] || !framebuffer[2])) return set_error(SCN_EINVAL, "render: scene.nee needs both shadow wavefronts and three framebuffer planes");
+    const size_t n_pixels = (size_t)tile_count * SCN_WF_TILE * SCN_WF_TILE;
+    if (n_pixels == 0 || spp_count == 0) return SCN_OK;
+    WfPaths W; if (int rc = wf_paths(paths, W, true)) return rc;
+    WfShadow L{}, Q{};
+    if (nee) {
+        if (int rc = wf_nee_arrays(paths)) return rc;
+        if (int rc = wf_shadow(light_rays, L)) return rc;
+        if (int rc = wf_shadow(phase_rays, Q)) return rc;
+    }
+    cudaStream_t s = (cudaStream_t)stream;
+    for (uint32_t done = 0; done < spp_count; done += spp_chunk) {
+        const uint32_t c = spp_count - done < spp_chunk ? spp_count - done : spp_chunk;
+        const size_t n = n_pixels * c;
+        const unsigned grid = (unsigned)((n + WF_BLOCK - 1) / WF_BLOCK);
+        if (int rc = scn_wf_raygen_strided(scene, m, tile_first, tile_stride, tile_count, spp_first + done, c, paths, n, stream)) return rc;
+        for (int32_t bounce = 0; bounce < scene->max_bounces; ++bounce) {
+            if (int rc = scn_sample_distance_batch(m, &paths->rays, &paths->state, &paths->samples, n, stream)) return rc;
+            const bool direct = nee && bounce < scene->max_bounces - 1; // volumeEstimateDirect at every scatter of this bounce (TraceBase.cpp:546)
+            if (direct) {
+                if (int rc = scn_wf_nee_setup(scene, m, paths, light_rays, phase_rays, n, bounce, stream)) return rc;
+                if (int rc = scn_transmittance_batch(m, &light_rays->rays, &light_rays->state, light_rays->T, n, stream)) return rc;
+                if (int rc = scn_transmittance_batch(m, &phase_rays->rays, &phase_rays->state, phase_rays->T, n, stream)) return rc;
+            }
+            if (!nee) k_wf_shade<<<grid, WF_BLOCK, 0, s>>>(*scene, W, bounce, n);
+            else if (direct) k_wf_shade_nee<true><<<grid, WF_BLOCK, 0, s>>>(*scene, W, L, Q, bounce, n);
+            else k_wf_shade_nee<false><<<grid, WF_BLOCK, 0, s>>>(*scene, W, L, Q, bounce, n);
+            if (int rc = wf_check("k_wf_shade")) return rc;
+        }
+        if (nee) if (int rc = scn_wf_clamp_samples(paths, n, stream)) return rc;
+        if (int rc = scn_wf_accumulate(paths->radiance, framebuffer[0], n_pixels, c, stream)) return rc;
+        if (nee) for (int j = 0; j < 2; ++j) if (int rc = scn_wf_accumulate(paths->radiance_gb[j], framebuffer[1 + j], n_pixels, c, stream)) return rc;
+    }
+    return SCN_OK;
 }
 
 } // extern "C"

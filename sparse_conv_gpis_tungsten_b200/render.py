@@ -51,6 +51,8 @@ RENDER_SYMBOLS = {
     "scn_wf_nee_setup": (C.c_int, [C.POINTER(WfScene), abi.MediumP, C.POINTER(WfPaths), C.POINTER(WfShadow), C.POINTER(WfShadow), C.c_size_t, C.c_int32, C.c_void_p]),
     "scn_wf_nee_gather": (C.c_int, [C.POINTER(WfPaths), C.POINTER(WfShadow), C.POINTER(WfShadow), C.c_size_t, C.c_void_p]),
     "scn_wf_clamp_samples": (C.c_int, [C.POINTER(WfPaths), C.c_size_t, C.c_void_p]),
+    "scn_wf_render": (C.c_int, [C.POINTER(WfScene), abi.MediumP, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.POINTER(WfPaths),
+                                C.POINTER(WfShadow), C.POINTER(WfShadow), C.POINTER(abi.f32p * 3), C.c_void_p]),
 }
 
 
@@ -236,14 +238,27 @@ class WavefrontRenderer:
         if self.n_pixels:
             self._alloc(self.n_pixels * max(1, min(spp, self.max_paths // self.n_pixels)))
 
-    def render(self, spp, count_queries=False):
+    def render(self, spp, count_queries=False, stepwise=False):
         """Add `spp` samples per pixel to this rank's framebuffer slice.  Samples are processed in chunks so that a wavefront
-        holds at most max_paths paths."""
+        holds at most max_paths paths.  The loop over chunks and bounces runs inside the library (scn_wf_render: one call, no host
+        synchronisation); `stepwise` (and `count_queries`, which needs a host read per bounce) drives the same kernels launch by
+        launch through the per-stage entry points instead — the tests compare the two."""
         if self.n_pixels == 0:
             return
         stream = torch.cuda.current_stream(self.dev)
         sp = C.c_void_p(stream.cuda_stream)
         chunk = max(1, min(spp, self.max_paths // self.n_pixels))
+        if not (count_queries or stepwise):
+            self._alloc(self.n_pixels * chunk)
+            fbs = (abi.f32p * 3)()
+            planes = [self.framebuffer] + (self.framebuffer_gb if self.nee else [])
+            for j, fb in enumerate(planes):
+                fbs[j] = C.cast(C.c_void_p(fb.data_ptr()), abi.f32p)
+            L, Q = (self.shadow if self.nee else (None, None))
+            abi.check(self.lib.scn_wf_render(C.byref(self.scene), self.medium._h, self.tile_first, self.tile_stride, self.tile_count, self.spp_done, spp, chunk,
+                                             C.byref(self.paths), C.byref(L["c"]) if L else None, C.byref(Q["c"]) if Q else None, C.byref(fbs), sp))
+            self.spp_done += spp
+            return
         done = 0
         while done < spp:
             c = min(chunk, spp - done)
@@ -290,37 +305,41 @@ def assemble_image(tiles, res_x, res_y):
 
 
 def gather_image_rgb(renderer, world=1):
-    """[res_y, res_x, 3]: three gather_image calls for an nee (RGB) render, the grey image repeated otherwise."""
+    """[res_y, res_x, 3] on every rank with ONE all_gather: the three planes of an nee (RGB) render travel stacked; a grey render
+    gathers its one plane and repeats it."""
     if not getattr(renderer, "nee", False):
         g = gather_image(renderer, world)
         return torch.stack([g, g, g], -1)
-    return torch.stack([gather_image(renderer, world, ch) for ch in range(3)], -1)
+    local = torch.stack([renderer.local_image(ch) for ch in range(3)], 1)  # [tile_count, 3, 16, 16]
+    tiles = _gather_tiles(renderer, local, world)
+    return torch.stack([assemble_image(tiles[:, ch].contiguous(), renderer.scene.res_x, renderer.scene.res_y) for ch in range(3)], -1)
+
+
+def _gather_tiles(renderer, local, world):
+    """The one collective of a render: all ranks' framebuffer slices ([tile_count, ...] per rank) -> every tile in diceTiles order
+    on every rank (NCCL all_gather over NVLink).  Slices are padded to the largest tile count so that the gather is a single call."""
+    if world <= 1:
+        return local
+    import torch.distributed as dist
+    cap = (renderer.n_tiles + world - 1) // world
+    pad = torch.zeros((cap,) + tuple(local.shape[1:]), dtype=torch.float32, device=local.device)
+    pad[: local.shape[0]] = local
+    if dist.get_backend() == "nccl":
+        flat = torch.empty((world * cap,) + tuple(local.shape[1:]), dtype=torch.float32, device=local.device)
+        dist.all_gather_into_tensor(flat, pad)  # one NCCL all_gather straight into the assembled buffer
+        out = list(flat.view((world, cap) + tuple(local.shape[1:])).unbind(0))
+    else:
+        out = [torch.empty_like(pad) for _ in range(world)]
+        dist.all_gather(out, pad)
+    if getattr(renderer, "sharding", "contiguous") == "interleaved":  # tile t lives at out[t % world][t // world]
+        return torch.stack(out, 1).reshape((world * cap,) + tuple(local.shape[1:]))[: renderer.n_tiles]
+    return torch.cat([out[r][: tile_range(renderer.n_tiles, r, world)[1]] for r in range(world)], 0)
 
 
 def gather_image(renderer, world=1, channel=0):
-    """The one collective of a render: all ranks' framebuffer slices -> the full image on every rank (NCCL all_gather over
-    NVLink; 4 B per pixel).  Slices are padded to the largest tile count so that the gather is a single call."""
+    """One plane of the image on every rank ([res_y, res_x]; 4 B per pixel through the all_gather)."""
     local = renderer.local_image(channel) if channel else renderer.local_image()
-    if world > 1:
-        import torch.distributed as dist
-        cap = (renderer.n_tiles + world - 1) // world
-        pad = torch.zeros(cap, TILE, TILE, dtype=torch.float32, device=local.device)
-        pad[: local.shape[0]] = local
-        if dist.get_backend() == "nccl":
-            flat = torch.empty(world * cap, TILE, TILE, dtype=torch.float32, device=local.device)
-            dist.all_gather_into_tensor(flat, pad)  # one NCCL all_gather straight into the assembled buffer
-            out = list(flat.view(world, cap, TILE, TILE).unbind(0))
-        else:
-            out = [torch.empty_like(pad) for _ in range(world)]
-            dist.all_gather(out, pad)
-        if getattr(renderer, "sharding", "contiguous") == "interleaved":  # tile t lives at out[t % world][t // world]
-            tiles = torch.stack(out, 1).reshape(world * cap, TILE, TILE)[: renderer.n_tiles]
-        else:
-            parts = [out[r][: tile_range(renderer.n_tiles, r, world)[1]] for r in range(world)]
-            tiles = torch.cat(parts, 0)
-    else:
-        tiles = local
-    return assemble_image(tiles, renderer.scene.res_x, renderer.scene.res_y)
+    return assemble_image(_gather_tiles(renderer, local, world), renderer.scene.res_x, renderer.scene.res_y)
 
 
 def write_pfm(path, img):
