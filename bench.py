@@ -245,9 +245,82 @@ def run_gpu(args):
     e2e_value = world * ne * e2e_steps / float(te.item())
     same = all(torch.equal(a, b[:ne].cpu()) for a, b in zip(ho, outs))
 
-    # ---- tile-sharded wavefront renders: every rank renders its contiguous tile range, one NCCL all_gather of the slices.
-    #      C1 = Appendix A.1 without next-event estimation; C4 = Appendix A.3 (copper conductor phase bsdf, quad light, NEE + MIS)
-    render, render_c4, render_c5 = None, None, None
+    # ---- end to end with PAGEABLE host buffers (what a caller gets who does not page-lock: every cudaMemcpyAsync is staged by the driver)
+    e2e_pageable = None
+    if not args.no_extras:
+        npg = min(ne, 1 << 24)
+        pp = [x[:npg].cpu() for x in P]; pd_ = [x[:npg].cpu() for x in D]; po = [torch.empty(npg) for _ in range(4)]
+        med.eval_noise_into(pp, pd_, 1, po)
+        t0 = time.perf_counter()
+        med.eval_noise_into(pp, pd_, 1, po)
+        torch.cuda.synchronize()
+        e2e_pageable = {"value": npg / (time.perf_counter() - t0), "unit": UNIT, "points_per_step": npg, "note": "rank 0's figure; ordinary (pageable) numpy/torch host memory"}
+        del pp, pd_, po
+
+    # ---- medium queries / s (BASELINE metric, first half): 2^20 rays through the Appendix-A cube per BASELINE render config, primary
+    #      (camera rays) and secondary (rays carrying Renewal state), median of 5 launches, device-resident; and the same C1 wavefront
+    #      end to end through scn_sample_distance_batch_host from pinned host SoA buffers (max over ranks)
+    queries, e2e_queries = None, None
+    if not args.no_extras:
+        queries = {}
+        nq = 1 << 20
+        for key, name in (("C1", "c1_sphere_3d_none"), ("C3", "c3_1d_renewal"), ("C4", "c4_1d_renewalplus_xy_mis"), ("C5", "c5_multires_nonstat_renewalplus")):
+            g = S.GpuImpl(S.MEDIA[name], device=local)
+            row = {"medium": name, "kernel": g.m.info()["query_kernel"], "rays": nq}
+            for secondary in (False, True):
+                rr, ss = S.camera_rays(nq, seed=11, secondary=secondary)
+                r, s_ = g._rays_state(rr, ss)
+                out = g.m.sample_distance(r, s_, scene_seed=1, count_evals=True)
+                torch.cuda.synchronize()
+                times = []
+                for _ in range(5):
+                    r, s_ = g._rays_state(rr, ss)
+                    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                    a.record(stream); out = g.m.sample_distance(r, s_, scene_seed=1, out=out, stream=stream); b.record(stream); torch.cuda.synchronize()
+                    times.append(a.elapsed_time(b) * 1e-3)
+                qs = float(np.median(times))
+                tq = torch.tensor([qs], device=dev, dtype=torch.float64)
+                if world > 1:
+                    dist.all_reduce(tq, op=dist.ReduceOp.MAX)
+                qs = float(tq.item())
+                ev = int(out["n_evals"].view(torch.int32).to(torch.int64).sum().item())
+                tag = "secondary" if secondary else "primary"
+                row[tag + "_queries_per_s"] = world * nq / qs
+                row[tag + "_noise_evals_per_s"] = world * ev / qs
+                row[tag + "_evals_per_query"] = ev / nq
+                if not secondary:
+                    out_primary = {"t": out["t"].clone()}
+            queries[key] = row
+            if key == "C1":  # end to end: pinned host SoA -> scn_sample_distance_batch_host -> pinned host SoA
+                gh = S.GpuImpl(S.MEDIA[name], device=local, host=True)
+                rr, ss = S.camera_rays(nq, seed=11)
+                hr0, hs0 = gh._rays_state(rr, ss)  # numpy SoA
+                pin = lambda a_: torch.from_numpy(a_.view(np.int32) if a_.dtype == np.uint32 else a_).pin_memory()
+                hr = {k: pin(v) for k, v in hr0.items()}
+                tdt = {np.float32: torch.float32, np.int32: torch.int32, np.uint8: torch.uint8}
+                from sparse_conv_gpis_tungsten_b200.medium import SAMPLE_FIELDS
+                ho_q = {k: torch.empty(nq, dtype=tdt[dt]).pin_memory() for k, dt in SAMPLE_FIELDS}
+                tt = []
+                for k in range(4):
+                    hs = {kk: pin(v.copy()) for kk, v in hs0.items()}  # the state is updated in place: a fresh copy per step
+                    if world > 1:
+                        dist.barrier()
+                    t0 = time.perf_counter()
+                    gh.m.sample_distance(hr, hs, scene_seed=1, out=ho_q)
+                    tt.append(time.perf_counter() - t0)
+                te2 = torch.tensor([float(np.median(tt[1:]))], device=dev, dtype=torch.float64)
+                if world > 1:
+                    dist.all_reduce(te2, op=dist.ReduceOp.MAX)
+                nbytes = lambda d_: int(sum(v.numel() * v.element_size() for v in d_.values()))
+                e2e_queries = {"value": world * nq / float(te2.item()), "unit": "queries/s", "h2d_bytes_per_step": nbytes(hr) + nbytes({k: v for k, v in hs.items() if k != "scheme" and not k.startswith("ctx_")}),
+                               "d2h_bytes_per_step": nbytes(ho_q) + nbytes(hs), "rays_per_step": nq, "matches_device": bool(torch.equal(ho_q["t"], out_primary["t"].cpu())),
+                               "api": "scn_sample_distance_batch_host (C1 medium, 2^20 camera rays; pinned host SoA rays + state in, samples + state out; one stream per stage)"}
+                gh.close()
+            g.close()
+
+    # ---- tile-sharded wavefront renders at the BASELINE.json sizes: every rank renders its tiles (round-robin ownership), one NCCL
+    #      all_gather of the slices.  Strong scaling: the same image at every N.
+    renders = None
     if not args.no_extras:
         from sparse_conv_gpis_tungsten_b200 import render as R
 
@@ -264,18 +337,22 @@ def run_gpu(args):
             if world > 1:
                 dist.all_reduce(tr, op=dist.ReduceOp.MAX)
             res = sc["camera"]["resolution"]
-            out = {"workload": "%s %dx%d @%dspp, max_bounces %d, nee %s, 16x16 tiles sharded over %d GPU(s) (%s), one all_gather" % (label, res[0], res[1], spp, sc["integrator"]["max_bounces"], "on" if wr.nee else "off", world, wr.sharding),
-                   "ms": float(tr.item()), "camera_paths_per_s": res[0] * res[1] * spp / (float(tr.item()) * 1e-3), "mean_radiance": float(img.mean().item())}
+            out = {"workload": "%s %dx%d @%dspp, max_bounces %d, nee %s, 16x16 tiles over %d GPU(s) (%s), one all_gather" % (label, res[0], res[1], spp, sc["integrator"]["max_bounces"], "on" if wr.nee else "off", world, wr.sharding),
+                   "ms": float(tr.item()), "camera_paths": res[0] * res[1] * spp, "camera_paths_per_s": res[0] * res[1] * spp / (float(tr.item()) * 1e-3), "mean_radiance": float(img.mean().item())}
             wr.close()
             return out
 
-        RES = 1024  # strong scaling over the GPUs: the same image at every N (16.8 M camera paths)
-        render = timed_render(S.appendix_a_scene(S.MEDIA["c1_sphere_3d_none"], RES, 16), 16, "C1 scene (Appendix A.1)")
-        render_c4 = timed_render(S.appendix_a_scene(S.c4_scene_medium(), RES, 16, quad=True), 16, "C4 scene (Appendix A.3: 1D Renewal+ XY, copper conductor, quad light, mis)")
-        render_c5 = timed_render(S.appendix_a_scene(S.MEDIA["c5_multires_nonstat_renewalplus"], RES, 16), 16, "C5 scene (Appendix A.4: multi-resolution non-stationary, renewal+)")
-        if world > 1:  # the contiguous ranges of SURVEY 8(e) next to the round-robin ownership used above
-            render["contiguous_ms"] = timed_render(S.appendix_a_scene(S.MEDIA["c1_sphere_3d_none"], RES, 16), 16, "C1", "contiguous")["ms"]
-            render_c5["contiguous_ms"] = timed_render(S.appendix_a_scene(S.MEDIA["c5_multires_nonstat_renewalplus"], RES, 16), 16, "C5", "contiguous")["ms"]
+        q = args.render_scale  # 1 = the BASELINE.json sizes; smaller values shrink the sample counts (developer runs), stated in the workload string
+        spp_of = lambda full: max(1, int(round(full * q)))
+        renders = {
+            "C1": timed_render(S.appendix_a_scene(S.MEDIA["c1_sphere_3d_none"], 256, 16), 16, "C1 scene (Appendix A.1)"),
+            "C3": timed_render(S.appendix_a_scene(S.MEDIA["c3_1d_renewal"], 512, spp_of(64)), spp_of(64), "C3 scene (Appendix A.2: 1D sampling, renewal, ensemble)"),
+            "C4": timed_render(S.appendix_a_scene(S.c4_scene_medium(), 1024, spp_of(128), quad=True), spp_of(128), "C4 scene (Appendix A.3: 1D Renewal+ XY, copper conductor, quad light, mis)"),
+            "C5": timed_render(S.appendix_a_scene(S.MEDIA["c5_multires_nonstat_renewalplus"], 2048, spp_of(256)), spp_of(256), "C5 scene (Appendix A.4: multi-resolution non-stationary, renewal+)"),
+        }
+        if world > 1:  # the contiguous ranges of SURVEY 8(e) next to the round-robin ownership used above, C5 scene at 1/16 of the samples
+            sc5 = S.appendix_a_scene(S.MEDIA["c5_multires_nonstat_renewalplus"], 2048, 16)
+            renders["C5_sharding"] = {"interleaved_ms": timed_render(sc5, 16, "C5", "interleaved")["ms"], "contiguous_ms": timed_render(sc5, 16, "C5", "contiguous")["ms"], "workload": "C5 scene 2048x2048 @16spp"}
 
     if rank != 0:
         if world > 1:
@@ -310,12 +387,8 @@ def run_gpu(args):
                         "peak_source": "measured (MEASURED_PEAKS.json)" if "hbm_gbs" in peaks else "fallback"},
                 "peak_source": "SMs x 4 schedulers x 32 lanes x SM clock sampled during the timed region (SURVEY.md 8(d)); sm_count=%d, MHz=%.0f" % (sms, f_mhz)}
 
-    # ---- extras: density sweep, world space, medium queries / s (configs[0]-style rays); one pass each, outside the timed region
-    extra = {"e2e_matches_device": bool(same)}
-    if render is not None:
-        extra["render"] = render
-        extra["render_c4"] = render_c4
-        extra["render_c5"] = render_c5
+    # ---- density sweep of the microbench (BASELINE configs[1]: impulse_density 1-64, isotropic vs world space); one timed pass each
+    sweep = None
     if not args.no_extras:
         sweep = {}
         for iso in (True, False):
@@ -328,53 +401,37 @@ def run_gpu(args):
                 ev = n / (a.elapsed_time(b) * 1e-3)
                 sweep["%s_N%d" % ("iso" if iso else "world", dens)] = {"evals_per_s": ev, "issue_frac": ev * w_issue(dens) / issue_peak}
                 m2.close()
-        extra["sweep"] = sweep
-        # medium queries (sampleDistance): 2^20 camera rays through the Appendix-A cube, one medium per BASELINE render config
-        nq = 1 << 20
-        rays, st = S.camera_rays(nq, seed=11)
-        for key, name, what in (("medium_queries", "c1_sphere_3d_none", "C1 medium (sphere mean, SE, 3D iso, none/single)"),
-                                ("medium_queries_c3", "c3_1d_renewal", "C3 medium (1D sampling, renewal)"),
-                                ("medium_queries_c4", "c4_1d_renewalplus_xy_mis", "C4 medium (1D sampling, renewal+, correlationXY, mis)"),
-                                ("medium_queries_c5", "c5_multires_nonstat_renewalplus", "C5 medium (multi-resolution non-stationary, renewal+)")):
-            g = S.GpuImpl(S.MEDIA[name], device=local)
-            for secondary in (False, True):  # camera rays (first scatter) and rays that carry Renewal state from a previous vertex
-                rr, ss = S.camera_rays(nq, seed=11, secondary=secondary)
-                r, s_ = g._rays_state(rr, ss)
-                out = g.m.sample_distance(r, s_, scene_seed=1, count_evals=True)
-                torch.cuda.synchronize()
-                r, s_ = g._rays_state(rr, ss)
-                a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-                a.record(stream); out = g.m.sample_distance(r, s_, scene_seed=1, out=out, stream=stream); b.record(stream); torch.cuda.synchronize()
-                qs = a.elapsed_time(b) * 1e-3
-                ev = int(out["n_evals"].view(torch.int32).to(torch.int64).sum().item())
-                row = {"queries_per_s": nq / qs, "noise_evals_per_s": ev / qs, "evals_per_query": ev / nq}
-                if not secondary:
-                    extra[key] = dict({"workload": what + ", 2^20 camera rays, step 0.01"}, **row)
-                else:
-                    extra[key]["secondary"] = row
-            g.close()
-        extra["medium_queries"]["kernel"] = "k_march (cached wavefront march)"
 
-    # ---- CPU baseline on this box's host cores (bounded sample)
+    # ---- what ncu counted for each kernel family (committed captures, profiles/ncu_issue_active.json): the model fraction above charges
+    #      SURVEY's frozen 6090 lane-ops per evaluation, the kernel executes fewer; for the march kernels only the ncu figure applies
+    ncu_counted = None
+    try:
+        ncu_counted = json.load(open(os.path.join(ROOT, "profiles", "ncu_issue_active.json")))
+    except Exception:
+        pass
+    if ncu_counted:
+        roofline["issue_active_ncu"] = {k: v.get("issue_active_pct") for k, v in ncu_counted.items() if isinstance(v, dict)}
+        kf = ncu_counted.get(roofline["kernel"])
+        if kf and kf.get("lane_instr_per_eval"):
+            roofline["frac_ncu_counted"] = per_gpu * kf["lane_instr_per_eval"] / issue_peak
+            roofline["note"] = "frac = SURVEY 8(d) model (6090 lane-ops/eval, frozen); frac_ncu_counted = the %d lane-instructions/eval ncu counted x this run's rate; issue_active_ncu = smsp__issue_active of the committed captures" % kf["lane_instr_per_eval"]
+
+    # ---- CPU baseline on this box's host cores (bounded samples)
     threads = os.cpu_count() or 1
-    if render is not None and S.have_ref():
+    if renders is not None and S.have_ref():
         # the reference's own multithreaded renderer (Scene::load -> PathTraceIntegrator through oracle/ref_harness.cpp: ref_render) on a
-        # bounded sample of the same scene: 64x64 @4spp, all host threads
-        try:
-            ref_paths_s, ref_sec = cpu_reference_render(S.appendix_a_scene(S.MEDIA["c1_sphere_3d_none"], 64, 4), threads)
-            render["cpu_reference"] = {"camera_paths_per_s": ref_paths_s, "cores": threads, "seconds": ref_sec, "kind": "reference",
-                                       "sample": "the same scene at 64x64 @4spp through the unmodified reference renderer (NEE on, scene_bvh off)"}
-            render["speedup_vs_cpu_reference"] = render["camera_paths_per_s"] / ref_paths_s
-            ref_paths_s, ref_sec = cpu_reference_render(S.appendix_a_scene(S.c4_scene_medium(), 64, 16, quad=True), threads)
-            render_c4["cpu_reference"] = {"camera_paths_per_s": ref_paths_s, "cores": threads, "seconds": ref_sec, "kind": "reference",
-                                          "sample": "the same scene at 64x64 @16spp through the unmodified reference renderer"}
-            render_c4["speedup_vs_cpu_reference"] = render_c4["camera_paths_per_s"] / ref_paths_s
-            ref_paths_s, ref_sec = cpu_reference_render(S.appendix_a_scene(S.MEDIA["c5_multires_nonstat_renewalplus"], 48, 4), threads)
-            render_c5["cpu_reference"] = {"camera_paths_per_s": ref_paths_s, "cores": threads, "seconds": ref_sec, "kind": "reference",
-                                          "sample": "the same scene at 48x48 @4spp through the unmodified reference renderer"}
-            render_c5["speedup_vs_cpu_reference"] = render_c5["camera_paths_per_s"] / ref_paths_s
-        except Exception as ex:  # the checker must never take the bench line down
-            render["cpu_reference"] = {"unavailable": str(ex)[:200]}
+        # bounded sample of each scene, all host threads
+        for key, sc, what in (("C1", S.appendix_a_scene(S.MEDIA["c1_sphere_3d_none"], 64, 4), "64x64 @4spp"),
+                              ("C3", S.appendix_a_scene(S.MEDIA["c3_1d_renewal"], 64, 16), "64x64 @16spp"),
+                              ("C4", S.appendix_a_scene(S.c4_scene_medium(), 64, 16, quad=True), "64x64 @16spp"),
+                              ("C5", S.appendix_a_scene(S.MEDIA["c5_multires_nonstat_renewalplus"], 48, 4), "48x48 @4spp")):
+            try:
+                ref_paths_s, ref_sec = cpu_reference_render(sc, threads)
+                renders[key]["cpu_reference"] = {"camera_paths_per_s": ref_paths_s, "cores": threads, "seconds": ref_sec, "kind": "reference",
+                                                 "sample": "the same scene at %s through the unmodified reference renderer (scene_bvh off)" % what}
+                renders[key]["speedup_vs_cpu_reference"] = renders[key]["camera_paths_per_s"] / ref_paths_s
+            except Exception as ex:  # the checker must never take the bench line down
+                renders[key]["cpu_reference"] = {"unavailable": str(ex)[:200]}
     impl, kind = cpu_impl(mj, threads)
     cs = 1 << 22
     cp, cd = host_points(cs)
@@ -386,17 +443,29 @@ def run_gpu(args):
     gd = [torch.from_numpy(np.ascontiguousarray(cd[:65536, j])).to(dev) for j in range(3)]
     go = torch.stack(med.eval_noise(gp, gd, 1), 1).cpu().numpy()
     want = impl.eval_noise(np.ascontiguousarray(cp[:65536]), np.ascontiguousarray(cd[:65536]), 1)
-    extra["parity_vs_cpu_max_rel_err"] = float(S.rel_err(go, want).max())
+    parity = float(S.rel_err(go, want).max())
 
+    config = {"workload": workload_name(), "points_per_gpu_per_step": n, "impulse_density": DENSITY, "isotropic_3D_sampling": ISO,
+              "l2": "inputs (%.1f GB) and outputs (%.1f GB) per step exceed the 126 MB L2" % (24 * n / 1e9, 16 * n / 1e9), "parallelism": "replicas x%d (weak)" % world,
+              "parity_vs_cpu_max_rel_err": parity}
+    if queries is not None:  # the other half of BASELINE's metric: medium queries / s per render config (whole job: all ranks' rays / max time)
+        config["medium_queries"] = queries
+    if renders is not None:  # strong scaling: the same image at every N
+        config["renders"] = renders
+    if sweep is not None:
+        config["density_sweep"] = sweep
+    e2e = {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": 24 * ne, "d2h_bytes_per_step": 16 * ne, "points_per_step": ne, "matches_device": bool(same),
+           "api": "scn_eval_batch_host (pinned host buffers; H2D, kernel and D2H each on their own stream, chunks chained by events)"}
+    if e2e_pageable is not None:
+        e2e["pageable"] = e2e_pageable
+    if e2e_queries is not None:
+        e2e["queries"] = e2e_queries
+    launches = args.steps
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
             "ms_per_step": ms_max / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": workload_name(), "points_per_gpu_per_step": n, "impulse_density": DENSITY, "isotropic_3D_sampling": ISO,
-                       "l2": "inputs (%.1f GB) and outputs (%.1f GB) per step exceed the 126 MB L2" % (24 * n / 1e9, 16 * n / 1e9), "parallelism": "replicas x%d (weak)" % world},
-            "clocks": clocks, "roofline": roofline,
+            "config": config, "clocks": clocks, "roofline": roofline,
             "cpu_baseline": {"value": cpu_v, "unit": UNIT, "cores": threads, "kind": kind, "sample": "first 2^22 of the 2^26 points, value+gradient, one pass"},
-            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": 24 * ne, "d2h_bytes_per_step": 16 * ne, "points_per_step": ne,
-                    "api": "scn_eval_batch_host (pinned host buffers; H2D, kernel and D2H each on their own stream, chunks chained by events)"},
-            "gpu_launches": args.steps, "extra": extra}
+            "e2e": e2e, "gpu_launches": launches}
     if world > 1:
         dist.destroy_process_group()
     return line
@@ -426,6 +495,7 @@ def main():
     ap.add_argument("--points", type=int, default=N_POINTS)
     ap.add_argument("--e2e-points", type=int, default=N_POINTS)
     ap.add_argument("--no-extras", action="store_true")
+    ap.add_argument("--render-scale", type=float, default=1.0, help="1 = BASELINE.json sample counts (C3 64, C4 128, C5 256 spp); smaller for developer runs")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
