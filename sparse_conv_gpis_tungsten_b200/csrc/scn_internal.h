@@ -67,6 +67,9 @@ struct Params {
     float mL[9], mW[9], mC[9], _pad3;
     double mC_dsi;             // 1 / sqrt(det mC) (GPF:749), host libm
     float log_base;            // logf(2.5f) from the host libm
+    // fp32 copies for k_march's fast multi-resolution level estimate (level_ratio_fast, scn_march.cuh): the single-ramp "ls" field
+    // as 0.5 log2(e) (la + r (lb - la)), r = clamp(c ls_f_scale + ls_f_off); 1 / log2(2.5)
+    float ls_f_a, ls_f_b, ls_f_scale, ls_f_off, inv_log2_base;
     // alternative stationary splat kernels (math/GPFunctions.cpp:1020-1082, 1127-1214): world-space sampling only
     int32_t kernel;            // SCN_COV_SQUARED_EXPONENTIAL | SCN_COV_MATERN | SCN_COV_GABOR_ANISO | SCN_COV_GABOR_ISO
     float k_v, k_l;            // Matern: _v, _l

@@ -119,6 +119,8 @@ int params_from_desc(const scn_medium_desc &d, Params &p) {
     // sparseConvNoiseMaxAnisotropyScale = max(a, 1/a) with _anisotropyOnAxis = 1.5 (GPF:1741-1745, GPF.hpp:2372)
     const float aniso_max = p.has_aniso ? 1.5f : 1.f;
     p.log_base = std::log(2.5f);
+    p.ls_f_a = (float)(0.5 * 1.4426950408889634 * p.ls.la[0]); p.ls_f_b = (float)(0.5 * 1.4426950408889634 * (p.ls.lb[0] - p.ls.la[0]));
+    p.ls_f_scale = (float)p.ls.scale[0]; p.ls_f_off = (float)p.ls.off[0]; p.inv_log2_base = (float)(1.0 / std::log2(2.5));
     p.world_scale = p.stationary ? 1.f : p.ls_max;
     p.add_seed_world = (int)std::floor(std::log(p.world_scale) / std::log(2.5f));
     p.R_iso = d.kernel_scale;
