@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define SCN_ABI_VERSION 4
+#define SCN_ABI_VERSION 5
 
 /* error codes */
 #define SCN_OK 0
@@ -71,6 +71,12 @@ extern "C" {
 #define SCN_FIELD_LEFT_RIGHT 3
 #define SCN_FIELD_FRONT_BACK 4
 #define SCN_FIELD_BOTTOM_TOP_LEFT_RIGHT 5
+#define SCN_FIELD_REGULAR_GRID 6 /* "type":"regular_grid" (RegularGridScalar / RegularGridVector, math/GPFunctions.hpp:429-578) */
+
+/* RegularGrid<ElemType>::interp (math/GPFunctions.hpp:241-306; strings of grids/Grid.cpp:6-26) */
+#define SCN_INTERP_POINT 0
+#define SCN_INTERP_LINEAR 1
+#define SCN_INTERP_QUADRATIC 2
 
 /* mean function: math/GPFunctions.hpp:867-1005 */
 typedef struct scn_mean_desc {
@@ -85,13 +91,27 @@ typedef struct scn_mean_desc {
     int32_t _pad;
 } scn_mean_desc;
 
-/* procedural scalar/vector field: "type":"constant"|"noise" (math/GPFunctions.cpp:53-138) */
+/* RegularGrid<double> / RegularGrid<Vec3d> (math/GPFunctions.hpp:241-330): a dense res^3 array over `bounds`, element
+ * (x res + y) res + z (:255-258), looked up by point / trilinear / triquadratic interpolation in double (:284-306).
+ * `values` is a HOST pointer to res^3 doubles (scalar field) or 3 res^3 doubles (vector field, xyz interleaved like the reference's
+ * "-values.bin" file); scn_medium_create copies it to the device, the caller keeps ownership — except for grids that
+ * scn_desc_from_json_at loaded from disk (`owned` = 1), which scn_desc_release frees. */
+typedef struct scn_grid_desc {
+    const double *values;
+    double bounds_min[3], bounds_max[3]; /* "bounds_min" "bounds_max" */
+    uint32_t res;                        /* "res"                      */
+    int32_t interp;                      /* "interpolate": SCN_INTERP_*, default linear */
+    int32_t owned, _pad;
+} scn_grid_desc;
+
+/* procedural scalar/vector field: "type":"constant"|"noise"|"regular_grid" (math/GPFunctions.cpp:53-138, GPFunctions.hpp:429-578) */
 typedef struct scn_field_desc {
     int32_t type;        /* SCN_FIELD_*                                              */
     int32_t _pad;
     double val[3];       /* constant: "val" (scalar fields use val[0])               */
     double min, max, start, end;      /* noise ramps: "min" "max" "start" "end"      */
     double min2, max2, start2, end2;  /* bottom_top_left_right second ramp           */
+    scn_grid_desc grid;  /* regular_grid: "file" -> grid JSON + binary values (appended in ABI version 5) */
 } scn_field_desc;
 
 /* Flattened JSON of one "sparse_conv_noise" medium and its "gaussian_process".
@@ -230,6 +250,12 @@ int scn_abi_version(void);
  * Unknown keys (phase_function, transmittance, name, ...) are ignored like the reference does. */
 int scn_desc_default(scn_medium_desc *desc);
 int scn_desc_from_json(const char *medium_json, scn_medium_desc *desc);
+/* The same with the directory that relative resource paths ("file" of a regular_grid field, then "path" inside the grid JSON relative
+ * to that file) resolve against, like Scene::fetchResource does against the scene file's directory (io/Scene.cpp, load_grid:
+ * math/GPFunctions.hpp:386-401).  scn_desc_from_json uses the current directory.  Grids are read into malloc'ed host arrays owned by
+ * the descriptor: call scn_desc_release when the descriptor is no longer needed (after scn_medium_create; a no-op otherwise). */
+int scn_desc_from_json_at(const char *medium_json, const char *base_dir, scn_medium_desc *desc);
+void scn_desc_release(scn_medium_desc *desc);
 
 /* MediumFactory "sparse_conv_noise" + prepareForRender (media/MediumFactory.cpp:13-22,
  * media/GaussianProcessMedium.cpp:152-158).  `device` is the CUDA ordinal that owns the medium. */

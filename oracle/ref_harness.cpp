@@ -346,6 +346,9 @@ int ref_nee(void *h, size_t n, const float *ray_dir, const float *normal, const 
 // The scene must set "renderer": {"scene_bvh": false}: TraceableScene then intersects its primitives in a plain loop
 // (renderer/TraceableScene.hpp:186-193) and embree — which this recipe does not build — is never entered.
 // Returns 0, or -1 with ref_last_error() set; *w and *h are written even when rgb is too small (cap < w*h*3).
+static bool g_save_outputs = false;
+// 1: ref_render also lets the reference write its result files (renderer.output_file / hdr_output_file, relative to the scene file)
+void ref_render_save_outputs(int on) { g_save_outputs = on != 0; }
 int ref_render(const char *scene_path, int threads, uint32_t seed, int *w, int *h, float *rgb, size_t cap, double *seconds) {
     try {
         static bool started = false;
@@ -369,6 +372,7 @@ int ref_render(const char *scene_path, int threads, uint32_t seed, int *w, int *
             integrator.waitForCompletion();
         }
         if (seconds) *seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+        if (g_save_outputs) integrator.saveOutputs(); // Integrator::writeBuffers (integrators/Integrator.cpp:40-64): the scene's output_file / hdr_output_file
         Vec2u res = flat->cam().resolution();
         *w = (int)res.x(); *h = (int)res.y();
         if (!rgb || cap < (size_t)res.product() * 3) { g_err = "rgb buffer too small"; return -1; }

@@ -186,6 +186,7 @@ orc_medium *orc_medium_create(const scn_medium_desc *desc) {
     if (!m->stationary && desc->ls.type != SCN_FIELD_NONE) {
         const scn_field_desc *f = &desc->ls;
         if (f->type == SCN_FIELD_CONSTANT) { double v = f->val[0] > f->val[1] ? f->val[0] : f->val[1]; v = v > f->val[2] ? v : f->val[2]; m->ls_max = (float)v; }
+        else if (f->type == SCN_FIELD_REGULAR_GRID) m->ls_max = 1.f; /* the reference's maxVal() of a grid field is 0 (GPF.hpp:474-477): multi-resolution form only, which never reads it */
         else if (f->type == SCN_FIELD_BOTTOM_TOP_LEFT_RIGHT) m->ls_max = (float)((f->max > f->min ? f->max : f->min) * (f->max2 > f->min2 ? f->max2 : f->min2));
         else m->ls_max = (float)(f->max > f->min ? f->max : f->min);
     }
@@ -211,8 +212,39 @@ static double field_ramp(const scn_field_desc *f, d3 p, int second) {
         return sqrt(exp(lerpd(log(mn * mn), log(mx * mx), clampd(p.x * scale + off, 0.0, 1.0))));
     }
 }
+/* RegularGrid<ElemType>::getValue (GPF.hpp:255-306): component c of ncomp interleaved doubles; trilinearInterpolation (:173-188),
+ * triquadraticInterpolation (:190-230), lerp = a (1 - t) + b t (math/MathUtil.hpp:91-94) */
+static double grid_at(const scn_grid_desc *g, int ncomp, int x, int y, int z, int c) {
+    int r = (int)g->res;
+    x = x < 0 ? 0 : (x > r - 1 ? r - 1 : x); y = y < 0 ? 0 : (y > r - 1 ? r - 1 : y); z = z < 0 ? 0 : (z > r - 1 ? r - 1 : z);
+    return g->values[((size_t)(x * r + y) * r + z) * ncomp + c];
+}
+static double quadd(double v0, double v1, double v2, double w) { double a = 0.5 * (v0 + v2) - v1, b = 0.5 * (v2 - v0); return w * (w * a + b) + v1; }
+static double field_grid(const scn_grid_desc *g, int ncomp, d3 p, int c) {
+    double res = (double)g->res;
+    double gx = (res * (p.x - g->bounds_min[0])) / (g->bounds_max[0] - g->bounds_min[0]) - 0.5;
+    double gy = (res * (p.y - g->bounds_min[1])) / (g->bounds_max[1] - g->bounds_min[1]) - 0.5;
+    double gz = (res * (p.z - g->bounds_min[2])) / (g->bounds_max[2] - g->bounds_min[2]) - 0.5;
+    int ix = (int)floor(gx), iy = (int)floor(gy), iz = (int)floor(gz);
+    double u = gx - (double)ix, v = gy - (double)iy, w = gz - (double)iz;
+    if (g->interp == SCN_INTERP_POINT) return grid_at(g, ncomp, ix, iy, iz, c);
+    if (g->interp == SCN_INTERP_LINEAR) {
+        double z0 = lerpd(lerpd(grid_at(g, ncomp, ix, iy, iz, c), grid_at(g, ncomp, ix + 1, iy, iz, c), u), lerpd(grid_at(g, ncomp, ix, iy + 1, iz, c), grid_at(g, ncomp, ix + 1, iy + 1, iz, c), u), v);
+        double z1 = lerpd(lerpd(grid_at(g, ncomp, ix, iy, iz + 1, c), grid_at(g, ncomp, ix + 1, iy, iz + 1, c), u), lerpd(grid_at(g, ncomp, ix, iy + 1, iz + 1, c), grid_at(g, ncomp, ix + 1, iy + 1, iz + 1, c), u), v);
+        return lerpd(z0, z1, w);
+    }
+    double vx[3];
+    for (int dx = 0; dx < 3; ++dx) {
+        double vy[3];
+        for (int dy = 0; dy < 3; ++dy)
+            vy[dy] = quadd(grid_at(g, ncomp, ix - 1 + dx, iy - 1 + dy, iz - 1, c), grid_at(g, ncomp, ix - 1 + dx, iy - 1 + dy, iz, c), grid_at(g, ncomp, ix - 1 + dx, iy - 1 + dy, iz + 1, c), w);
+        vx[dx] = quadd(vy[0], vy[1], vy[2], v);
+    }
+    return quadd(vx[0], vx[1], vx[2], u);
+}
 static double field_scalar(const scn_field_desc *f, d3 p) {
     switch (f->type) {
+    case SCN_FIELD_REGULAR_GRID: return field_grid(&f->grid, 1, p, 0); /* RegularGridScalar (GPF.hpp:429-437) */
     case SCN_FIELD_CONSTANT: return f->val[0];
     case SCN_FIELD_BOTTOM_TOP: case SCN_FIELD_LEFT_RIGHT: case SCN_FIELD_FRONT_BACK: return field_ramp(f, p, 0) - 1.;
     case SCN_FIELD_BOTTOM_TOP_LEFT_RIGHT: { float bt = (float)field_ramp(f, p, 0), lr = (float)field_ramp(f, p, 1); return bt * lr - 1. * 1.; }
@@ -222,6 +254,7 @@ static double field_scalar(const scn_field_desc *f, d3 p) {
 static d3 field_vector(const scn_field_desc *f, d3 p) {
     d3 r;
     if (f->type == SCN_FIELD_CONSTANT) { r.x = f->val[0]; r.y = f->val[1]; r.z = f->val[2]; return r; }
+    if (f->type == SCN_FIELD_REGULAR_GRID) { r.x = field_grid(&f->grid, 3, p, 0); r.y = field_grid(&f->grid, 3, p, 1); r.z = field_grid(&f->grid, 3, p, 2); return r; } /* RegularGridVector (GPF.hpp:504-512) */
     double v = field_scalar(f, p); r.x = r.y = r.z = v; return r;
 }
 

@@ -23,9 +23,19 @@ class MeanDesc(C.Structure):
                 ("ref", C.c_double * 3), ("dir", C.c_double * 3), ("min", C.c_float), ("_pad", C.c_int32)]
 
 
+FIELD_REGULAR_GRID = 6
+INTERP_POINT, INTERP_LINEAR, INTERP_QUADRATIC = 0, 1, 2
+
+
+class GridDesc(C.Structure):
+    _fields_ = [("values", C.POINTER(C.c_double)), ("bounds_min", C.c_double * 3), ("bounds_max", C.c_double * 3), ("res", C.c_uint32),
+                ("interp", C.c_int32), ("owned", C.c_int32), ("_pad", C.c_int32)]
+
+
 class FieldDesc(C.Structure):
     _fields_ = [("type", C.c_int32), ("_pad", C.c_int32), ("val", C.c_double * 3), ("min", C.c_double), ("max", C.c_double),
-                ("start", C.c_double), ("end", C.c_double), ("min2", C.c_double), ("max2", C.c_double), ("start2", C.c_double), ("end2", C.c_double)]
+                ("start", C.c_double), ("end", C.c_double), ("min2", C.c_double), ("max2", C.c_double), ("start2", C.c_double), ("end2", C.c_double),
+                ("grid", GridDesc)]
 
 
 class MediumDesc(C.Structure):
@@ -86,6 +96,8 @@ SYMBOLS = {
     "scn_abi_version": (C.c_int, []),
     "scn_desc_default": (C.c_int, [C.POINTER(MediumDesc)]),
     "scn_desc_from_json": (C.c_int, [C.c_char_p, C.POINTER(MediumDesc)]),
+    "scn_desc_from_json_at": (C.c_int, [C.c_char_p, C.c_char_p, C.POINTER(MediumDesc)]),
+    "scn_desc_release": (None, [C.POINTER(MediumDesc)]),
     "scn_medium_create": (C.c_int, [C.POINTER(MediumDesc), C.c_int, C.POINTER(MediumP)]),
     "scn_medium_destroy": (None, [MediumP]),
     "scn_eval_batch": (C.c_int, [MediumP, C.POINTER(EvalIn), C.POINTER(EvalOut), C.c_size_t, C.c_int, C.c_void_p]),
@@ -127,7 +139,7 @@ def load():
         fn = getattr(lib, name)  # AttributeError if the symbol is not exported
         fn.restype = res
         fn.argtypes = args
-    if lib.scn_abi_version() != 4:
+    if lib.scn_abi_version() != 5:
         raise ImportError("libscn_b200.so ABI version mismatch")
     _lib = lib
     return lib

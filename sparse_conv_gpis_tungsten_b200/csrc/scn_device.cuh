@@ -134,8 +134,44 @@ SCN_HD double field_ramp(const FieldK &k, double c, int second) {
     double r = yadd(ymul(c, k.scale[second]), k.off[second]); r = r > 0.0 ? r : 0.0; r = r < 1.0 ? r : 1.0;
     return sqrt(exp(yadd(ymul(k.la[second], ysub(1.0, r)), ymul(k.lb[second], r))));
 }
+// RegularGrid<ElemType>::getValue (math/GPFunctions.hpp:255-306), component `c` of `ncomp` interleaved ones, in double like the reference:
+// p_grid = res (p - min) / diagonal - 0.5, clamped integer coordinates, element (x res + y) res + z; point, trilinear (lerp = a (1 - t) + b t,
+// math/MathUtil.hpp:91-94, x innermost then y then z: GPFunctions.hpp:173-188) or triquadratic (z, then y, then x: :190-230) interpolation.
+SCN_HD double grid_at(const FieldK &k, int x, int y, int z, int c) {
+    const int r = k.gres;
+    x = x < 0 ? 0 : (x > r - 1 ? r - 1 : x); y = y < 0 ? 0 : (y > r - 1 ? r - 1 : y); z = z < 0 ? 0 : (z > r - 1 ? r - 1 : z);
+    return k.grid[((size_t)(x * r + y) * r + z) * k.gcomp + c];
+}
+SCN_HD double lerp_d(double a, double b, double t) { return yadd(ymul(a, ysub(1.0, t)), ymul(b, t)); }
+SCN_HD double quad_d(double v0, double v1, double v2, double w) { // _interpolate (GPFunctions.hpp:193-202)
+    const double a = ysub(ymul(0.5, yadd(v0, v2)), v1), b = ymul(0.5, ysub(v2, v0));
+    return yadd(ymul(w, yadd(ymul(w, a), b)), v1);
+}
+SCN_FN double field_grid(const FieldK &k, dbl3 p, int c) {
+    const double res = (double)k.gres;
+    const double gx = ysub(ydiv(ymul(res, ysub(p.x, k.gmin[0])), k.gdiag[0]), 0.5), gy = ysub(ydiv(ymul(res, ysub(p.y, k.gmin[1])), k.gdiag[1]), 0.5),
+                 gz = ysub(ydiv(ymul(res, ysub(p.z, k.gmin[2])), k.gdiag[2]), 0.5);
+    const double fx = floor(gx), fy = floor(gy), fz = floor(gz);
+    const int ix = (int)fx, iy = (int)fy, iz = (int)fz;
+    const double u = ysub(gx, (double)ix), v = ysub(gy, (double)iy), w = ysub(gz, (double)iz);
+    if (k.ginterp == SCN_INTERP_POINT) return grid_at(k, ix, iy, iz, c);
+    if (k.ginterp == SCN_INTERP_LINEAR) {
+        const double z0 = lerp_d(lerp_d(grid_at(k, ix, iy, iz, c), grid_at(k, ix + 1, iy, iz, c), u), lerp_d(grid_at(k, ix, iy + 1, iz, c), grid_at(k, ix + 1, iy + 1, iz, c), u), v);
+        const double z1 = lerp_d(lerp_d(grid_at(k, ix, iy, iz + 1, c), grid_at(k, ix + 1, iy, iz + 1, c), u), lerp_d(grid_at(k, ix, iy + 1, iz + 1, c), grid_at(k, ix + 1, iy + 1, iz + 1, c), u), v);
+        return lerp_d(z0, z1, w);
+    }
+    double vx[3];
+    for (int dx = 0; dx < 3; ++dx) {
+        double vy[3];
+        for (int dy = 0; dy < 3; ++dy)
+            vy[dy] = quad_d(grid_at(k, ix - 1 + dx, iy - 1 + dy, iz - 1, c), grid_at(k, ix - 1 + dx, iy - 1 + dy, iz, c), grid_at(k, ix - 1 + dx, iy - 1 + dy, iz + 1, c), w);
+        vx[dx] = quad_d(vy[0], vy[1], vy[2], v);
+    }
+    return quad_d(vx[0], vx[1], vx[2], u);
+}
 SCN_FN double field_scalar(const FieldK &k, dbl3 p) {
     switch (k.type) {
+    case SCN_FIELD_REGULAR_GRID: return field_grid(k, p, 0);
     case SCN_FIELD_CONSTANT: return k.val[0];
     case SCN_FIELD_BOTTOM_TOP: return field_ramp(k, p.y, 0) - 1.;
     case SCN_FIELD_LEFT_RIGHT: return field_ramp(k, p.x, 0) - 1.;
@@ -150,6 +186,10 @@ SCN_HD dbl3 to_dbl3(f3 p) { dbl3 r; r.x = p.x; r.y = p.y; r.z = p.z; return r; }
 SCN_HD float cov_lateral_scale(const Params &P, f3 p) { // sparseConvNoiseLateralScale
     if (P.stationary || P.ls.type == SCN_FIELD_NONE) return 1.0f;
     if (P.ls.type == SCN_FIELD_CONSTANT) return max3((float)P.ls.val[0], (float)P.ls.val[1], (float)P.ls.val[2]);
+    if (P.ls.type == SCN_FIELD_REGULAR_GRID) { // getKernelScale (GPF:1729-1735): Vec3f of the interpolated Vec3d, largest component
+        const dbl3 q = to_dbl3(p);
+        return max3((float)field_grid(P.ls, q, 0), (float)field_grid(P.ls, q, 1), (float)field_grid(P.ls, q, 2));
+    }
     return (float)field_scalar(P.ls, to_dbl3(p));
 }
 SCN_HD float cov_ns_scale(const Params &P, f3 p) { // nonStationarySplattingKernelScale

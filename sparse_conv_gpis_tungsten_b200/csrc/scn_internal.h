@@ -12,7 +12,8 @@ namespace scn {
 int set_error(int code, const char *fmt, ...);
 const char *last_error();
 int desc_default(scn_medium_desc *d);
-int desc_from_json(const char *text, scn_medium_desc *d);
+int desc_from_json(const char *text, const char *base_dir, scn_medium_desc *d);
+void desc_release(scn_medium_desc *d);
 
 // Multi-resolution levels k in [LVL_MIN, LVL_MIN + LVL_COUNT): scale = powf(2.5f, k) and the seed offset
 // floor(logf(scale)/logf(2.5f)) come out of the HOST libm (the reference derives an integer seed offset and
@@ -25,6 +26,9 @@ struct FieldK {
     int32_t type, _pad;
     double val[3];
     double la[2], lb[2], scale[2], off[2]; // [0] first ramp, [1] second ramp of bottom_top_left_right
+    // regular_grid (math/GPFunctions.hpp:241-330): res^3 x ncomp doubles — device memory inside the kernels, the caller's host array in
+    // params_from_desc and in tests/hostsim; bounds and the diagonal as the reference's getValue reads them
+    const double *grid; double gmin[3], gdiag[3]; int32_t gres, ginterp, gcomp, _pad2;
 };
 
 // Everything a kernel needs, derived once from scn_medium_desc in scn_medium_create (device copy lives in

@@ -12,6 +12,7 @@
 #include <cfloat>
 #include <cmath>
 #include <cstdlib>
+#include <cstdio>
 #include <cstring>
 #include <map>
 #include <memory>
@@ -140,9 +141,55 @@ int parseMean(const JVal &j, scn_mean_desc &m) {
     return SCN_OK;
 }
 
+thread_local std::string g_base_dir; // directory relative resource paths resolve against (scn_desc_from_json_at)
+
+std::string joinPath(const std::string &dir, const std::string &rel) {
+    if (rel.empty() || rel[0] == '/' || dir.empty()) return rel;
+    return dir.back() == '/' ? dir + rel : dir + "/" + rel;
+}
+std::string parentDir(const std::string &path) { size_t k = path.find_last_of('/'); return k == std::string::npos ? std::string() : path.substr(0, k); }
+bool readFile(const std::string &path, std::string &out) {
+    FILE *fp = fopen(path.c_str(), "rb"); if (!fp) return false;
+    char buf[1 << 16]; size_t k;
+    while ((k = fread(buf, 1, sizeof buf, fp)) > 0) out.append(buf, k);
+    fclose(fp); return true;
+}
+// RegularGridScalar / RegularGridVector::fromJson + loadResources -> load_grid (math/GPFunctions.hpp:386-401, 358-369, 335-344):
+// "file" names a grid JSON {bounds_min, bounds_max, res, interpolate, path}; "path", relative to that file, holds the raw doubles.
+int loadGrid(const JVal &j, scn_field_desc &f, bool vector) {
+    std::string file;
+    if (!getS(j, "file", file)) return set_error(SCN_EJSON, "regular_grid field: missing \"file\"");
+    const std::string gpath = joinPath(g_base_dir, file);
+    std::string text;
+    if (!readFile(gpath, text)) return set_error(SCN_EJSON, "regular_grid field: cannot read '%s'", gpath.c_str());
+    Parser p(text.c_str()); JVal g;
+    if (!p.value(g) || g.kind != JVal::Obj) return set_error(SCN_EJSON, "regular_grid '%s': JSON parse error: %s", gpath.c_str(), p.err.c_str());
+    scn_grid_desc &G = f.grid;
+    getVec3(g, "bounds_min", G.bounds_min); getVec3(g, "bounds_max", G.bounds_max); getU(g, "res", G.res);
+    std::string interp = "linear";
+    getS(g, "interpolate", interp);
+    if (interp == "point") G.interp = SCN_INTERP_POINT; else if (interp == "linear") G.interp = SCN_INTERP_LINEAR;
+    else if (interp == "quadratic") G.interp = SCN_INTERP_QUADRATIC; else return set_error(SCN_EJSON, "Invalid interpolate method: '%s'", interp.c_str());
+    std::string vpath;
+    if (!getS(g, "path", vpath)) return set_error(SCN_EJSON, "regular_grid '%s': missing \"path\"", gpath.c_str());
+    vpath = joinPath(parentDir(gpath), vpath);
+    if (G.res == 0 || G.res > 2048) return set_error(SCN_EINVAL, "regular_grid '%s': res %u out of range", gpath.c_str(), G.res);
+    const size_t count = (size_t)G.res * G.res * G.res * (vector ? 3 : 1);
+    std::string raw;
+    if (!readFile(vpath, raw)) return set_error(SCN_EJSON, "regular_grid: cannot read values file '%s'", vpath.c_str());
+    if (raw.size() / sizeof(double) < count) return set_error(SCN_EINVAL, "regular_grid '%s': %zu values, res^3 needs %zu", vpath.c_str(), raw.size() / sizeof(double), count);
+    double *vals = (double *)malloc(count * sizeof(double));
+    if (!vals) return set_error(SCN_ENOMEM, "out of memory");
+    memcpy(vals, raw.data(), count * sizeof(double));
+    G.values = vals; G.owned = 1;
+    f.type = SCN_FIELD_REGULAR_GRID;
+    return SCN_OK;
+}
+
 int parseField(const JVal &j, scn_field_desc &f, bool vector) {
     std::string type;
     if (!getS(j, "type", type)) return set_error(SCN_EJSON, "procedural field: missing \"type\"");
+    if (type == "regular_grid") return loadGrid(j, f, vector);
     if (type == "constant") {
         f.type = SCN_FIELD_CONSTANT;
         if (vector) getVec3(j, "val", f.val); else { getD(j, "val", f.val[0]); f.val[1] = f.val[2] = f.val[0]; }
@@ -252,6 +299,7 @@ void meanDefault(scn_mean_desc &m) {
 void fieldDefault(scn_field_desc &f) {
     memset(&f, 0, sizeof f);
     f.type = SCN_FIELD_NONE; f.min = 1.; f.max = 500.; f.start = 0.; f.end = 1.; f.min2 = 1.; f.max2 = 500.; f.start2 = 0.; f.end2 = 1.;
+    f.grid.interp = SCN_INTERP_LINEAR; // RegularGrid::interp default (math/GPFunctions.hpp:243)
 }
 
 } // namespace
@@ -274,7 +322,21 @@ int desc_default(scn_medium_desc *d) {
     return SCN_OK;
 }
 
-int desc_from_json(const char *text, scn_medium_desc *d) {
+void desc_release(scn_medium_desc *d) {
+    if (!d) return;
+    for (scn_field_desc *f : {&d->ls, &d->var, &d->aniso_field})
+        if (f->grid.owned && f->grid.values) { free((void *)f->grid.values); f->grid.values = nullptr; f->grid.owned = 0; }
+}
+
+static int desc_from_json_impl(const char *text, scn_medium_desc *d);
+int desc_from_json(const char *text, const char *base_dir, scn_medium_desc *d) {
+    g_base_dir = base_dir ? base_dir : "";
+    int rc = desc_from_json_impl(text, d);
+    if (rc != SCN_OK && d) desc_release(d); // a grid read before the failing key
+    return rc;
+}
+
+static int desc_from_json_impl(const char *text, scn_medium_desc *d) {
     if (!text || !d) return set_error(SCN_EINVAL, "null argument");
     if (int rc = desc_default(d)) return rc;
     Parser p(text);

@@ -46,6 +46,17 @@ static void field_k(const scn_field_desc &f, FieldK &k) {
     double mn = f.min + c, mx = f.max + c, mn2 = f.min2 + c, mx2 = f.max2 + c;
     k.la[0] = std::log(mn * mn); k.lb[0] = std::log(mx * mx); k.scale[0] = 1.0 / (f.end - f.start); k.off[0] = -f.start * k.scale[0];
     k.la[1] = std::log(mn2 * mn2); k.lb[1] = std::log(mx2 * mx2); k.scale[1] = 1.0 / (f.end2 - f.start2); k.off[1] = -f.start2 * k.scale[1];
+    if (f.type == SCN_FIELD_REGULAR_GRID) { // Box3d::diagonal() = max - min (math/Box.hpp:62-65)
+        k.grid = f.grid.values; k.gres = (int32_t)f.grid.res; k.ginterp = f.grid.interp;
+        for (int i = 0; i < 3; ++i) { k.gmin[i] = f.grid.bounds_min[i]; k.gdiag[i] = f.grid.bounds_max[i] - f.grid.bounds_min[i]; }
+    }
+}
+static int check_grid(const scn_field_desc &f, const char *name) {
+    if (f.type != SCN_FIELD_REGULAR_GRID) return SCN_OK;
+    if (!f.grid.values) return set_error(SCN_EINVAL, "%s: regular_grid without values", name);
+    if (f.grid.res == 0 || f.grid.res > 2048) return set_error(SCN_EINVAL, "%s: regular_grid res %u out of range", name, f.grid.res);
+    if (f.grid.interp < SCN_INTERP_POINT || f.grid.interp > SCN_INTERP_QUADRATIC) return set_error(SCN_EINVAL, "%s: bad interpolate method", name);
+    return SCN_OK;
 }
 
 int params_from_desc(const scn_medium_desc &d, Params &p) {
@@ -109,9 +120,19 @@ int params_from_desc(const scn_medium_desc &d, Params &p) {
         const scn_field_desc &f = d.ls;
         if (f.type == SCN_FIELD_CONSTANT) p.ls_max = (float)std::fmax(std::fmax(f.val[0], f.val[1]), f.val[2]);
         else if (f.type == SCN_FIELD_BOTTOM_TOP_LEFT_RIGHT) p.ls_max = (float)(std::fmax(f.max, f.min) * std::fmax(f.max2, f.min2));
+        else if (f.type == SCN_FIELD_REGULAR_GRID) p.ls_max = 1.f; // accepted in the multi-resolution form only (below), which never reads it
         else p.ls_max = (float)std::fmax(f.max, f.min);
     }
+    if (int rc = check_grid(d.ls, "ls")) return rc;
+    if (int rc = check_grid(d.var, "var")) return rc;
+    if (int rc = check_grid(d.aniso_field, "aniso")) return rc;
+    // RegularGridVector does not override ProceduralVector::maxVal() (math/GPFunctions.hpp:474-477 prints "maxVal() not implemented!" and
+    // returns 0), so sparseConvNoiseMaxLateralScale() is 0 for a grid "ls" and the brute-force form divides by it (GPF:1227, 1246, 1262-1282):
+    // only the multi-resolution form, which never reads it, is defined behaviour in the reference
+    if (!p.stationary && d.ls.type == SCN_FIELD_REGULAR_GRID && !d.multires)
+        return set_error(SCN_EUNSUPPORTED, "\"ls\": regular_grid needs \"multiResolutionGrid\": true (the reference's maximum lateral scale of a grid field is 0: math/GPFunctions.hpp:474-477)");
     field_k(d.ls, p.ls); field_k(d.var, p.var); field_k(d.aniso_field, p.aniso_f);
+    p.ls.gcomp = 3; p.var.gcomp = 1; p.aniso_f.gcomp = 1;
     if (p.stationary) { p.ls.type = SCN_FIELD_NONE; p.var.type = SCN_FIELD_NONE; p.aniso_f.type = SCN_FIELD_NONE; }
     p.has_aniso = p.aniso_f.type != SCN_FIELD_NONE;
     if (p.has_aniso && d.sampling_1d)

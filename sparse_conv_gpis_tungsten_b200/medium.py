@@ -11,6 +11,7 @@ arena).  Nothing here computes: there is no fallback if the CUDA library is miss
 """
 import ctypes as C
 import json
+import os
 
 import numpy as np
 
@@ -142,20 +143,26 @@ class SparseConvolutionNoiseMedium:
 
     # ---- construction (fromJson) -------------------------------------------------------------------------------
     @staticmethod
-    def desc_from_json(medium_json):
-        """Parse the reference's medium JSON (a str or a dict) into a flat descriptor; raises ScnError like FAIL()."""
+    def desc_from_json(medium_json, base_dir=None):
+        """Parse the reference's medium JSON (a str or a dict) into a flat descriptor; raises ScnError like FAIL().  `base_dir` is the
+        directory relative resource paths (regular_grid "file") resolve against — the scene file's directory in Tungsten.  A descriptor
+        with regular_grid fields owns their host arrays: release it with scn_desc_release (from_json does)."""
         if not isinstance(medium_json, (str, bytes)):
             medium_json = json.dumps(medium_json)
         if isinstance(medium_json, str):
             medium_json = medium_json.encode()
         lib = abi.load()
         d = abi.MediumDesc()
-        abi.check(lib.scn_desc_from_json(medium_json, C.byref(d)))
+        abi.check(lib.scn_desc_from_json_at(medium_json, None if base_dir is None else os.fsencode(base_dir), C.byref(d)))
         return d
 
     @classmethod
-    def from_json(cls, medium_json, device=0):
-        return cls(cls.desc_from_json(medium_json), device)
+    def from_json(cls, medium_json, device=0, base_dir=None):
+        d = cls.desc_from_json(medium_json, base_dir)
+        try:
+            return cls(d, device)
+        finally:
+            abi.load().scn_desc_release(C.byref(d))  # the medium holds its own device copy of every grid
 
     def info(self):
         """scn_medium_info: which kernel family serves this medium ("k_march", "k_march1d", "generic"; "k_fast_noise3d" for the noise

@@ -342,10 +342,80 @@ def gather_image(renderer, world=1, channel=0):
     return assemble_image(_gather_tiles(renderer, local, world), renderer.scene.res_x, renderer.scene.res_y)
 
 
+def _as_rgb(img):
+    a = np.asarray(img.detach().cpu() if hasattr(img, "detach") else img, dtype=np.float32)
+    if a.ndim == 2:  # a grey render: the reference's framebuffer is RGB, the three channels are equal
+        a = np.repeat(a[:, :, None], 3, axis=2)
+    if a.ndim != 3 or a.shape[2] != 3:
+        raise ValueError("image must be [h, w] or [h, w, 3]")
+    return a
+
+
 def write_pfm(path, img):
-    """PFM writer matching the reference's HDR output (io/ImageIO.cpp savePfm): bottom-up rows, little-endian, 3 channels."""
-    a = np.asarray(img, dtype=np.float32)
-    rgb = np.repeat(a[::-1, :, None], 3, axis=2)
+    """The reference's HDR output (io/ImageIO.cpp:531-547 savePfm): "PF", "w h", "-1" (the stream prints -1.0 as -1), then the rows
+    bottom-up as little-endian float32 RGB.  `img` is [h, w, 3] (or [h, w] grey), top row first."""
+    a = _as_rgb(img)
     with open(path, "wb") as f:
-        f.write(b"PF\n%d %d\n-1.0\n" % (a.shape[1], a.shape[0]))
-        f.write(rgb.astype("<f4").tobytes())
+        f.write(b"PF\n%d %d\n-1\n" % (a.shape[1], a.shape[0]))
+        f.write(np.ascontiguousarray(a[::-1]).astype("<f4").tobytes())
+
+
+TONEMAPS = ("linear", "gamma", "reinhard", "filmic", "pbrt")
+
+
+def tonemap(img, op="gamma"):
+    """Camera::tonemap (cameras/Camera.hpp:159-162: negative values clamped to 0) over Tonemap::tonemap (cameras/Tonemap.hpp:25-50), float32
+    like the reference (powf: evaluated in double and rounded, which is what glibc's powf does)."""
+    c = np.maximum(_as_rgb(img), np.float32(0))
+    f32 = np.float32
+    pw = lambda x, e: np.power(x.astype(np.float64), float(f32(e))).astype(np.float32)
+    if op == "linear":
+        return c
+    if op == "gamma":
+        return pw(c, f32(1.0) / f32(2.2))
+    if op == "reinhard":
+        return pw(c / (c + f32(1.0)), f32(1.0) / f32(2.2))
+    if op == "filmic":
+        x = np.maximum(f32(0), c - f32(0.004))
+        return (x * (f32(6.2) * x + f32(0.5))) / (x * (f32(6.2) * x + f32(1.7)) + f32(0.06))
+    if op == "pbrt":
+        return np.where(c < f32(0.0031308), f32(12.92) * c, f32(1.055) * pw(c, f32(1.0) / f32(2.4)) - f32(0.055)).astype(np.float32)
+    raise ValueError("Invalid tonemap operator: '%s'" % op)
+
+
+def to_ldr(img, op="gamma"):
+    """Integrator::writeBuffers (integrators/Integrator.cpp:50-51): Vec3c(clamp(Vec3i(tonemap(c) * 255.0f), 0, 255)) — truncation, not rounding."""
+    t = tonemap(img, op) * np.float32(255.0)
+    t = np.where(np.isfinite(t), t, np.where(t > 0, np.float32(2e9), np.float32(-2e9)))  # int conversion of +-inf / NaN is undefined in the reference; clamp like 0 / 255
+    return np.clip(t.astype(np.int64), 0, 255).astype(np.uint8)
+
+
+def write_png(path, img, op="gamma"):
+    """The reference's LDR output (io/ImageIO.cpp:590-611 savePng over Integrator.cpp:50-56): 8-bit RGB of the tonemapped image.  The
+    encoder differs from lodepng (zlib stream, filter choice), the decoded pixels do not."""
+    import struct
+    import zlib
+    ldr = to_ldr(img, op)
+    h, w = ldr.shape[:2]
+    raw = b"".join(b"\x00" + ldr[y].tobytes() for y in range(h))  # filter type 0 on every scanline
+    chunk = lambda tag, data: struct.pack(">I", len(data)) + tag + data + struct.pack(">I", zlib.crc32(tag + data) & 0xFFFFFFFF)
+    with open(path, "wb") as f:
+        f.write(b"\x89PNG\r\n\x1a\n" + chunk(b"IHDR", struct.pack(">IIBBBBB", w, h, 8, 2, 0, 0, 0)) + chunk(b"IDAT", zlib.compress(raw, 9)) + chunk(b"IEND", b""))
+
+
+def write_outputs(scene_json, img, directory="."):
+    """Integrator::saveOutputs for a finished render: renderer.output_file (PNG, the camera's "tonemap" operator, default "gamma":
+    cameras/Camera.cpp:22) and renderer.hdr_output_file (PFM) relative to `directory`, like the reference writes them next to the
+    scene file.  Returns the paths written."""
+    import os
+    r = scene_json.get("renderer", {})
+    out = []
+    if r.get("output_file"):
+        if not r["output_file"].lower().endswith(".png"):
+            raise ValueError("output_file: only PNG is covered (io/ImageIO.cpp:625-631)")
+        write_png(os.path.join(directory, r["output_file"]), img, scene_json.get("camera", {}).get("tonemap", "gamma")); out.append(os.path.join(directory, r["output_file"]))
+    if r.get("hdr_output_file"):
+        if not r["hdr_output_file"].lower().endswith(".pfm"):
+            raise ValueError("hdr_output_file: only PFM is covered (OpenEXR is not built: io/ImageIO.cpp:613-623)")
+        write_pfm(os.path.join(directory, r["hdr_output_file"]), img); out.append(os.path.join(directory, r["hdr_output_file"]))
+    return out

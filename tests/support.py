@@ -66,6 +66,12 @@ def _nonstat(multires=True, **kw):
     return c
 
 
+def _grid(name):
+    """A regular_grid field over tests/golden/grids/<name>.json (absolute path: the reference resolves "file" against the scene's directory,
+    the harness has none)."""
+    return {"type": "regular_grid", "file": os.path.join(GOLDEN_DIR, "grids", name + ".json")}
+
+
 # a rotated, sheared anisotropy matrix (row-major), well conditioned
 _MTX_COV = {"type": "squared_exponential", "sigma": 0.05, "lengthScale": 0.1, "aniso": [1, 1, 1], "useAnisoMtx": True,
             "anisoMtx": [1.2, 0.3, -0.1, -0.2, 0.8, 0.25, 0.15, -0.1, 1.1]}
@@ -129,6 +135,14 @@ MEDIA = {
     "aniso_mtx_1d_xy_mis": medium(correlation_context="renewal+", single_realization=False, covariance=dict(_MTX_COV),
                                   **{"1D_sampling": True, "1D_sampling_scheme": "mis", "1D_gradient_correlationXY": True}),
     "aniso_mtx_multires_iso": medium(correlation_context="renewal+", single_realization=False, covariance=_nonstat(True, cov=dict(_MTX_COV))),
+    # "regular_grid" procedural fields (math/GPFunctions.hpp:241-330, 429-578): dense res^3 arrays read from disk, point / trilinear /
+    # triquadratic lookup in double.  A grid "ls" exists in the multi-resolution form only (the reference's maxVal() of a grid field is 0).
+    "grid_var_bruteforce_iso": medium(correlation_context="renewal+", single_realization=False, covariance=_nonstat(False, var=_grid("var8_linear"))),
+    "grid_ls_multires_iso": medium(correlation_context="renewal+", single_realization=False, covariance=_nonstat(True, ls=_grid("ls6_quadratic"))),
+    "grid_ls_var_multires_1d": medium(correlation_context="renewal+", single_realization=False, covariance=_nonstat(True, ls=_grid("ls7_linear"), var=_grid("var5_quadratic")),
+                                      **{"1D_sampling": True, "1D_sampling_scheme": "mis", "1D_gradient_correlationXY": True}),
+    "grid_aniso_var_world": medium(isotropic_3D_sampling=False, correlation_context="renewal", single_realization=False,
+                                   covariance=_nonstat(False, aniso=_grid("aniso4_point"), var=_grid("var5_quadratic"))),
 }
 IS_1D = {k: bool(v.get("1D_sampling")) for k, v in MEDIA.items()}
 
@@ -505,7 +519,7 @@ def ref_gpu_medium_stats(reset=False):
 # ------------------------------------------------------------------------------------------------ large-sample query parity
 PARITY_MEDIA = ["c1_sphere_3d_none", "c3_1d_renewal", "c4_1d_renewalplus_xy_mis", "c5_multires_nonstat_renewalplus", "iso_3d_renewalplus_aniso",
                 "world_3d_renewalplus", "multires_world", "nonstat_bruteforce_iso", "nonstat_bruteforce_world_var", "nonstat_bruteforce_1d_renewalplus",
-                "multires_1d_xy", "multires_1d_renewal"]
+                "multires_1d_xy", "multires_1d_renewal", "grid_var_bruteforce_iso", "grid_ls_multires_iso", "grid_ls_var_multires_1d"]
 
 
 def checker(medium_json):

@@ -18,7 +18,7 @@ def test_header_symbols_exported(built_library):
     assert declared == set(abi.SYMBOLS), declared ^ set(abi.SYMBOLS)
     for name in declared:
         assert hasattr(built_library, name)
-    assert built_library.scn_abi_version() == 4
+    assert built_library.scn_abi_version() == 5
 
 
 def test_desc_layout_and_defaults(built_library):
@@ -91,6 +91,37 @@ def test_unsupported_configurations_are_refused_not_approximated():
         Medium.desc_from_json("{ not json")
     with pytest.raises(abi.ScnError):
         MediumFactory.create({"type": "voxel"})
+
+
+def test_regular_grid_fields_load_like_the_reference():
+    """"regular_grid" fields (math/GPFunctions.hpp:346-401): "file" resolves against the base directory, "path" inside the grid JSON
+    against that file's directory; values arrive as res^3 (x3 for the vector field) doubles owned by the descriptor until released."""
+    import ctypes as C
+    import os
+    import numpy as np
+    gdir = os.path.join(S.GOLDEN_DIR, "grids")
+    mj = S.medium(covariance=S._nonstat(True, ls={"type": "regular_grid", "file": "ls6_quadratic.json"}, var={"type": "regular_grid", "file": "var8_linear.json"}))
+    d = Medium.desc_from_json(mj, base_dir=gdir)
+    try:
+        assert d.ls.type == abi.FIELD_REGULAR_GRID and d.ls.grid.res == 6 and d.ls.grid.interp == abi.INTERP_QUADRATIC and d.ls.grid.owned == 1
+        assert d.var.grid.res == 8 and d.var.grid.interp == abi.INTERP_LINEAR and list(d.var.grid.bounds_min) == [-1.6] * 3
+        got = np.ctypeslib.as_array(d.ls.grid.values, shape=(6 * 6 * 6 * 3,))
+        assert np.array_equal(got, np.fromfile(os.path.join(gdir, "ls6_quadratic-values.bin"), "<f8"))
+    finally:
+        abi.load().scn_desc_release(C.byref(d))
+    assert d.ls.grid.owned == 0 and not d.ls.grid.values
+    with pytest.raises(abi.ScnError) as e:  # relative path without its directory
+        Medium.desc_from_json(mj, base_dir="/nonexistent")
+    assert e.value.code == abi.SCN_EJSON and "cannot read" in str(e.value)
+    # a grid "ls" in the brute-force form: the reference's maximum lateral scale of a grid field is 0 (GPFunctions.hpp:474-477) -> refused
+    bad = S.medium(covariance=S._nonstat(False, ls={"type": "regular_grid", "file": "ls6_quadratic.json"}))
+    db = Medium.desc_from_json(bad, base_dir=gdir)
+    try:
+        with pytest.raises(abi.ScnError) as e:
+            Medium(db)
+        assert e.value.code == abi.SCN_EUNSUPPORTED and "multiResolutionGrid" in str(e.value)
+    finally:
+        abi.load().scn_desc_release(C.byref(db))
 
 
 def test_no_cpu_fallback():
