@@ -366,7 +366,11 @@ TONEMAPS = ("linear", "gamma", "reinhard", "filmic", "pbrt")
 def tonemap(img, op="gamma"):
     """Camera::tonemap (cameras/Camera.hpp:159-162: negative values clamped to 0) over Tonemap::tonemap (cameras/Tonemap.hpp:25-50), float32
     like the reference (powf: evaluated in double and rounded, which is what glibc's powf does)."""
-    c = np.maximum(_as_rgb(img), np.float32(0))
+    with np.errstate(invalid="ignore", over="ignore", divide="ignore"):  # inf / NaN radiance propagates like in the reference
+        return _tonemap(np.maximum(_as_rgb(img), np.float32(0)), op)
+
+
+def _tonemap(c, op):
     f32 = np.float32
     pw = lambda x, e: np.power(x.astype(np.float64), float(f32(e))).astype(np.float32)
     if op == "linear":
