@@ -53,6 +53,7 @@ extern "C" {
 #define SCN_MEAN_HOMOGENEOUS 0
 #define SCN_MEAN_SPHERICAL 1
 #define SCN_MEAN_LINEAR 2
+#define SCN_MEAN_PROCEDURAL 3 /* "procedural": ProceduralMean over an SDF function or a procedural scalar field, finite-difference gradient */
 
 /* CovarianceFunctionFactory strings, math/GaussianProcessFactory.cpp:25-38 (covered subset) */
 #define SCN_COV_SQUARED_EXPONENTIAL 0
@@ -78,18 +79,6 @@ extern "C" {
 #define SCN_INTERP_LINEAR 1
 #define SCN_INTERP_QUADRATIC 2
 
-/* mean function: math/GPFunctions.hpp:867-1005 */
-typedef struct scn_mean_desc {
-    int32_t type;        /* SCN_MEAN_*                                               */
-    float offset;        /* homogeneous: "offset"                                    */
-    double center[3];    /* spherical: "center"                                      */
-    float radius;        /* spherical: "radius"                                      */
-    float scale;         /* linear: "scale"                                          */
-    double ref[3];       /* linear: "reference_point"                                */
-    double dir[3];       /* linear: "direction" (normalised at parse time)           */
-    float min;           /* linear: "min" (default -FLT_MAX)                         */
-    int32_t _pad;
-} scn_mean_desc;
 
 /* RegularGrid<double> / RegularGrid<Vec3d> (math/GPFunctions.hpp:241-330): a dense res^3 array over `bounds`, element
  * (x res + y) res + z (:255-258), looked up by point / trilinear / triquadratic interpolation in double (:284-306).
@@ -113,6 +102,29 @@ typedef struct scn_field_desc {
     double min2, max2, start2, end2;  /* bottom_top_left_right second ramp           */
     scn_grid_desc grid;  /* regular_grid: "file" -> grid JSON + binary values (appended in ABI version 5) */
 } scn_field_desc;
+
+/* SdfFunctions::Function (math/SdfFunctions.hpp:12-18) for "type":"procedural" means given by "func" */
+#define SCN_SDF_FIELD 0        /* no "func": the mean is the ProceduralScalar "f" (constant | noise | regular_grid)          */
+#define SCN_SDF_KNOB_INNER 1   /* "knob_inner": sphere of radius 0.75 in the 0.8-scaled frame (math/SdfFunctions.cpp:148-157) */
+#define SCN_SDF_TWO_SPHERES 2  /* "two_spheres" (math/SdfFunctions.cpp:181-183)                                               */
+#define SCN_SDF_PLANE 3        /* "plane": p.y (math/SdfFunctions.hpp:53)                                                     */
+
+/* mean function: math/GPFunctions.hpp:867-1005 (homogeneous, spherical, linear), :1049-1087 + math/GPFunctions.cpp:250-296 (procedural) */
+typedef struct scn_mean_desc {
+    int32_t type;        /* SCN_MEAN_*                                               */
+    float offset;        /* homogeneous, procedural: "offset"                        */
+    double center[3];    /* spherical: "center"                                      */
+    float radius;        /* spherical: "radius"                                      */
+    float scale;         /* linear, procedural: "scale"                              */
+    double ref[3];       /* linear: "reference_point"                                */
+    double dir[3];       /* linear: "direction" (normalised at parse time)           */
+    float min;           /* linear, procedural: "min" (default -FLT_MAX)             */
+    int32_t sdf_func;    /* procedural: SCN_SDF_* ("func"; SCN_SDF_FIELD when the mean is the field "f")                         */
+    /* procedural (appended in ABI version 5): the INVERSE of "transform" (Mat4f::invert, math/Mat4f.hpp:75-101), rows 0-2 of the 4 x 4
+     * matrix row-major — ProceduralMean::mean evaluates f(invConfigTransform.transformPoint(Vec3f(p))) * scale + offset, floored at min */
+    float inv_transform[12];
+    scn_field_desc f;    /* procedural: "f" (a scalar field: a regular_grid here is a tabulated signed-distance mean)             */
+} scn_mean_desc;
 
 /* Flattened JSON of one "sparse_conv_noise" medium and its "gaussian_process".
  * Keys and defaults: media/SparseConvolutionNoiseMedium.cpp:17-35,57-73,

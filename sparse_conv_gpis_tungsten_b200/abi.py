@@ -18,11 +18,6 @@ EVAL_NOISE, EVAL_VALUE, EVAL_GRADIENT = 1, 2, 4
 f32p, u32p, i32p, u8p = C.POINTER(C.c_float), C.POINTER(C.c_uint32), C.POINTER(C.c_int32), C.POINTER(C.c_uint8)
 
 
-class MeanDesc(C.Structure):
-    _fields_ = [("type", C.c_int32), ("offset", C.c_float), ("center", C.c_double * 3), ("radius", C.c_float), ("scale", C.c_float),
-                ("ref", C.c_double * 3), ("dir", C.c_double * 3), ("min", C.c_float), ("_pad", C.c_int32)]
-
-
 FIELD_REGULAR_GRID = 6
 INTERP_POINT, INTERP_LINEAR, INTERP_QUADRATIC = 0, 1, 2
 
@@ -36,6 +31,16 @@ class FieldDesc(C.Structure):
     _fields_ = [("type", C.c_int32), ("_pad", C.c_int32), ("val", C.c_double * 3), ("min", C.c_double), ("max", C.c_double),
                 ("start", C.c_double), ("end", C.c_double), ("min2", C.c_double), ("max2", C.c_double), ("start2", C.c_double), ("end2", C.c_double),
                 ("grid", GridDesc)]
+
+
+class MeanDesc(C.Structure):
+    _fields_ = [("type", C.c_int32), ("offset", C.c_float), ("center", C.c_double * 3), ("radius", C.c_float), ("scale", C.c_float),
+                ("ref", C.c_double * 3), ("dir", C.c_double * 3), ("min", C.c_float), ("sdf_func", C.c_int32), ("inv_transform", C.c_float * 12),
+                ("f", FieldDesc)]
+
+
+MEAN_PROCEDURAL = 3
+SDF_FIELD, SDF_KNOB_INNER, SDF_TWO_SPHERES, SDF_PLANE = 0, 1, 2, 3
 
 
 class MediumDesc(C.Structure):

@@ -123,24 +123,6 @@ template <typename T> void getVec3(const JVal &o, const char *k, T *dst) {
     if (v->kind == JVal::Arr && v->arr.size() >= 3) for (int i = 0; i < 3; ++i) if (v->arr[i].kind == JVal::Num) dst[i] = (T)v->arr[i].num;
 }
 
-int parseMean(const JVal &j, scn_mean_desc &m) {
-    std::string type;
-    if (!getS(j, "type", type)) return set_error(SCN_EJSON, "mean: missing \"type\"");
-    if (j.get("color") || j.get("emission")) return set_error(SCN_EUNSUPPORTED, "mean: procedural \"color\"/\"emission\" fields are host-side and not covered");
-    if (type == "homogeneous") { m.type = SCN_MEAN_HOMOGENEOUS; getF(j, "offset", m.offset); }
-    else if (type == "spherical") { m.type = SCN_MEAN_SPHERICAL; getVec3(j, "center", m.center); getF(j, "radius", m.radius); }
-    else if (type == "linear") {
-        m.type = SCN_MEAN_LINEAR; getVec3(j, "reference_point", m.ref); getVec3(j, "direction", m.dir); getF(j, "scale", m.scale); getF(j, "min", m.min);
-        // _dir.normalize() in double (math/GPFunctions.hpp:963, math/Vec.hpp:184-189)
-        double l2 = 0.; l2 += m.dir[0] * m.dir[0]; l2 += m.dir[1] * m.dir[1]; l2 += m.dir[2] * m.dir[2];
-        double inv = 1.0 / std::sqrt(l2);
-        for (int i = 0; i < 3; ++i) m.dir[i] *= inv;
-    } else if (type == "tabulated" || type == "mesh" || type == "procedural" || type == "neural")
-        return set_error(SCN_EUNSUPPORTED, "mean type '%s' needs grids/BVH/MLP and is not covered", type.c_str());
-    else return set_error(SCN_EJSON, "Invalid mean: '%s'", type.c_str());
-    return SCN_OK;
-}
-
 thread_local std::string g_base_dir; // directory relative resource paths resolve against (scn_desc_from_json_at)
 
 std::string joinPath(const std::string &dir, const std::string &rel) {
@@ -206,6 +188,98 @@ int parseField(const JVal &j, scn_field_desc &f, bool vector) {
     else return set_error(SCN_EJSON, "Invalid noise typ function: '%s'", noise.c_str());
     getD(j, "min", f.min); getD(j, "max", f.max); getD(j, "start", f.start); getD(j, "end", f.end);
     getD(j, "min2", f.min2); getD(j, "max2", f.max2); getD(j, "start2", f.start2); getD(j, "end2", f.end2);
+    return SCN_OK;
+}
+
+// JsonPtr::get(Mat4f &) (io/JsonPtr.cpp:108-183): sixteen numbers row-major, or {position, scale, rotation} — the default axes pass
+// gramSchmidt unchanged; look_at / up / explicit axes are not covered.  Float arithmetic in the reference's order.
+int parseTransform(const JVal &t, float M[16]) {
+    if (t.kind == JVal::Arr) {
+        if (t.arr.size() != 16) return set_error(SCN_EJSON, "Trying to parse a matrix, but this array has the wrong size (need 16 elements, received %zu)", t.arr.size());
+        for (int i = 0; i < 16; ++i) M[i] = (float)t.arr[i].num;
+        return SCN_OK;
+    }
+    if (t.kind != JVal::Obj) return set_error(SCN_EJSON, "Parameter has wrong type: Expecting a matrix value here");
+    if (t.get("look_at") || t.get("up") || t.get("x_axis") || t.get("y_axis") || t.get("z_axis"))
+        return set_error(SCN_EUNSUPPORTED, "transform: look_at / up / explicit axes are not covered (position, scale, rotation, or 16 numbers)");
+    float x[3] = {1, 0, 0}, y[3] = {0, 1, 0}, z[3] = {0, 0, 1}, pos[3] = {0, 0, 0}, sc[3], rot[3];
+    getVec3(t, "position", pos);
+    if (t.get("scale")) { sc[0] = sc[1] = sc[2] = 1.f; getVec3(t, "scale", sc); for (int i = 0; i < 3; ++i) { x[i] *= sc[0]; y[i] *= sc[1]; z[i] *= sc[2]; } }
+    if (t.get("rotation")) { // Mat4f::rotYXZ (math/Mat4f.cpp:118-130), then tform * axis (transformVector)
+        rot[0] = rot[1] = rot[2] = 0.f; getVec3(t, "rotation", rot);
+        float r[3]; for (int i = 0; i < 3; ++i) r[i] = rot[i] * 3.1415926536f / 180.0f;
+        const float c[3] = {std::cos(r[0]), std::cos(r[1]), std::cos(r[2])}, s[3] = {std::sin(r[0]), std::sin(r[1]), std::sin(r[2])};
+        const float R[9] = {c[1] * c[2] - s[1] * s[0] * s[2], -c[1] * s[2] - s[1] * s[0] * c[2], -s[1] * c[0],
+                            c[0] * s[2], c[0] * c[2], -s[0],
+                            s[1] * c[2] + c[1] * s[0] * s[2], -s[1] * s[2] + c[1] * s[0] * c[2], c[1] * c[0]};
+        auto apply = [&](float *v) { const float a = v[0], b = v[1], cc = v[2]; for (int i = 0; i < 3; ++i) v[i] = R[3 * i] * a + R[3 * i + 1] * b + R[3 * i + 2] * cc; };
+        apply(x); apply(y); apply(z);
+    }
+    const float out[16] = {x[0], y[0], z[0], pos[0], x[1], y[1], z[1], pos[1], x[2], y[2], z[2], pos[2], 0.f, 0.f, 0.f, 1.f};
+    memcpy(M, out, sizeof out);
+    return SCN_OK;
+}
+// Mat4f::invert (math/Mat4f.hpp:75-101): cofactors in the reference's term order, identity when the determinant is 0
+void mat4Invert(const float a[16], float out[16]) {
+    float inv[16];
+    inv[ 0] =  a[5]*a[10]*a[15] - a[5]*a[11]*a[14] - a[9]*a[6]*a[15] + a[9]*a[7]*a[14] + a[13]*a[6]*a[11] - a[13]*a[7]*a[10];
+    inv[ 1] = -a[1]*a[10]*a[15] + a[1]*a[11]*a[14] + a[9]*a[2]*a[15] - a[9]*a[3]*a[14] - a[13]*a[2]*a[11] + a[13]*a[3]*a[10];
+    inv[ 2] =  a[1]*a[ 6]*a[15] - a[1]*a[ 7]*a[14] - a[5]*a[2]*a[15] + a[5]*a[3]*a[14] + a[13]*a[2]*a[ 7] - a[13]*a[3]*a[ 6];
+    inv[ 3] = -a[1]*a[ 6]*a[11] + a[1]*a[ 7]*a[10] + a[5]*a[2]*a[11] - a[5]*a[3]*a[10] - a[ 9]*a[2]*a[ 7] + a[ 9]*a[3]*a[ 6];
+    inv[ 4] = -a[4]*a[10]*a[15] + a[4]*a[11]*a[14] + a[8]*a[6]*a[15] - a[8]*a[7]*a[14] - a[12]*a[6]*a[11] + a[12]*a[7]*a[10];
+    inv[ 5] =  a[0]*a[10]*a[15] - a[0]*a[11]*a[14] - a[8]*a[2]*a[15] + a[8]*a[3]*a[14] + a[12]*a[2]*a[11] - a[12]*a[3]*a[10];
+    inv[ 6] = -a[0]*a[ 6]*a[15] + a[0]*a[ 7]*a[14] + a[4]*a[2]*a[15] - a[4]*a[3]*a[14] - a[12]*a[2]*a[ 7] + a[12]*a[3]*a[ 6];
+    inv[ 8] =  a[4]*a[ 9]*a[15] - a[4]*a[11]*a[13] - a[8]*a[5]*a[15] + a[8]*a[7]*a[13] + a[12]*a[5]*a[11] - a[12]*a[7]*a[ 9];
+    inv[ 7] =  a[0]*a[ 6]*a[11] - a[0]*a[ 7]*a[10] - a[4]*a[2]*a[11] + a[4]*a[3]*a[10] + a[ 8]*a[2]*a[ 7] - a[ 8]*a[3]*a[ 6];
+    inv[ 9] = -a[0]*a[ 9]*a[15] + a[0]*a[11]*a[13] + a[8]*a[1]*a[15] - a[8]*a[3]*a[13] - a[12]*a[1]*a[11] + a[12]*a[3]*a[ 9];
+    inv[10] =  a[0]*a[ 5]*a[15] - a[0]*a[ 7]*a[13] - a[4]*a[1]*a[15] + a[4]*a[3]*a[13] + a[12]*a[1]*a[ 7] - a[12]*a[3]*a[ 5];
+    inv[11] = -a[0]*a[ 5]*a[11] + a[0]*a[ 7]*a[ 9] + a[4]*a[1]*a[11] - a[4]*a[3]*a[ 9] - a[ 8]*a[1]*a[ 7] + a[ 8]*a[3]*a[ 5];
+    inv[12] = -a[4]*a[ 9]*a[14] + a[4]*a[10]*a[13] + a[8]*a[5]*a[14] - a[8]*a[6]*a[13] - a[12]*a[5]*a[10] + a[12]*a[6]*a[ 9];
+    inv[13] =  a[0]*a[ 9]*a[14] - a[0]*a[10]*a[13] - a[8]*a[1]*a[14] + a[8]*a[2]*a[13] + a[12]*a[1]*a[10] - a[12]*a[2]*a[ 9];
+    inv[14] = -a[0]*a[ 5]*a[14] + a[0]*a[ 6]*a[13] + a[4]*a[1]*a[14] - a[4]*a[2]*a[13] - a[12]*a[1]*a[ 6] + a[12]*a[2]*a[ 5];
+    inv[15] =  a[0]*a[ 5]*a[10] - a[0]*a[ 6]*a[ 9] - a[4]*a[1]*a[10] + a[4]*a[2]*a[ 9] + a[ 8]*a[1]*a[ 6] - a[ 8]*a[2]*a[ 5];
+    const float det = a[0]*inv[0] + a[1]*inv[4] + a[2]*inv[8] + a[3]*inv[12];
+    if (det == 0.0f) { for (int i = 0; i < 16; ++i) out[i] = (i % 5 == 0) ? 1.f : 0.f; return; }
+    const float invDet = 1.0f / det;
+    for (int i = 0; i < 16; ++i) out[i] = inv[i] * invDet;
+}
+
+int parseMean(const JVal &j, scn_mean_desc &m) {
+    std::string type;
+    if (!getS(j, "type", type)) return set_error(SCN_EJSON, "mean: missing \"type\"");
+    if (j.get("color") || j.get("emission")) return set_error(SCN_EUNSUPPORTED, "mean: procedural \"color\"/\"emission\" fields are host-side and not covered");
+    if (type == "homogeneous") { m.type = SCN_MEAN_HOMOGENEOUS; getF(j, "offset", m.offset); }
+    else if (type == "spherical") { m.type = SCN_MEAN_SPHERICAL; getVec3(j, "center", m.center); getF(j, "radius", m.radius); }
+    else if (type == "linear") {
+        m.type = SCN_MEAN_LINEAR; getVec3(j, "reference_point", m.ref); getVec3(j, "direction", m.dir); getF(j, "scale", m.scale); getF(j, "min", m.min);
+        // _dir.normalize() in double (math/GPFunctions.hpp:963, math/Vec.hpp:184-189)
+        double l2 = 0.; l2 += m.dir[0] * m.dir[0]; l2 += m.dir[1] * m.dir[1]; l2 += m.dir[2] * m.dir[2];
+        double inv = 1.0 / std::sqrt(l2);
+        for (int i = 0; i < 3; ++i) m.dir[i] *= inv;
+    } else if (type == "procedural") { // ProceduralMean::fromJson (math/GPFunctions.cpp:250-266)
+        m.type = SCN_MEAN_PROCEDURAL;
+        float T[16] = {1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1}, inv[16];
+        if (const JVal *t = j.get("transform")) if (int rc = parseTransform(*t, T)) return rc;
+        mat4Invert(T, inv);
+        for (int i = 0; i < 12; ++i) m.inv_transform[i] = inv[i];
+        std::string fn = "knob";
+        if (getS(j, "func", fn)) {
+            if (fn == "knob_inner") m.sdf_func = SCN_SDF_KNOB_INNER; else if (fn == "two_spheres") m.sdf_func = SCN_SDF_TWO_SPHERES; else if (fn == "plane") m.sdf_func = SCN_SDF_PLANE;
+            else if (fn == "knob" || fn == "knob_outer") return set_error(SCN_EUNSUPPORTED, "procedural mean: the material-test knob ('%s') is not covered (knob_inner, two_spheres, plane and field means are)", fn.c_str());
+            else return set_error(SCN_EJSON, "Invalid function: '%s'", fn.c_str());
+        } else if (const JVal *f = j.get("f")) {
+            m.sdf_func = SCN_SDF_FIELD;
+            std::string ft; getS(*f, "type", ft);
+            if (ft == "sdf") { // ProceduralSdf (math/GPFunctions.hpp:579-603): the same function table
+                std::string fs; getS(*f, "function", fs);
+                if (fs == "knob_inner") m.sdf_func = SCN_SDF_KNOB_INNER; else if (fs == "two_spheres") m.sdf_func = SCN_SDF_TWO_SPHERES; else if (fs == "plane") m.sdf_func = SCN_SDF_PLANE;
+                else return set_error(SCN_EUNSUPPORTED, "procedural mean: sdf function '%s' is not covered", fs.c_str());
+            } else if (int rc = parseField(*f, m.f, false)) return rc;
+        } else return set_error(SCN_EUNSUPPORTED, "procedural mean without \"func\" or \"f\": the reference's default is the material-test knob, which is not covered");
+        getF(j, "min", m.min); getF(j, "scale", m.scale); getF(j, "offset", m.offset);
+    } else if (type == "tabulated" || type == "mesh" || type == "neural")
+        return set_error(SCN_EUNSUPPORTED, "mean type '%s' needs an OpenVDB grid / a mesh BVH / an MLP and is not covered", type.c_str());
+    else return set_error(SCN_EJSON, "Invalid mean: '%s'", type.c_str());
     return SCN_OK;
 }
 
@@ -292,9 +366,12 @@ int parseGP(const JVal &j, scn_medium_desc &d) {
     return set_error(SCN_EJSON, "Invalid gaussian_process: '%s'", type.c_str());
 }
 
+void fieldDefault(scn_field_desc &f);
 void meanDefault(scn_mean_desc &m) {
     memset(&m, 0, sizeof m);
     m.type = SCN_MEAN_SPHERICAL; m.radius = 1.f; m.scale = 1.f; m.dir[0] = 1.; m.min = -FLT_MAX;
+    m.inv_transform[0] = m.inv_transform[5] = m.inv_transform[10] = 1.f;
+    fieldDefault(m.f);
 }
 void fieldDefault(scn_field_desc &f) {
     memset(&f, 0, sizeof f);
@@ -324,7 +401,7 @@ int desc_default(scn_medium_desc *d) {
 
 void desc_release(scn_medium_desc *d) {
     if (!d) return;
-    for (scn_field_desc *f : {&d->ls, &d->var, &d->aniso_field})
+    for (scn_field_desc *f : {&d->ls, &d->var, &d->aniso_field, &d->mean.f, &d->mean_additional.f})
         if (f->grid.owned && f->grid.values) { free((void *)f->grid.values); f->grid.values = nullptr; f->grid.owned = 0; }
 }
 

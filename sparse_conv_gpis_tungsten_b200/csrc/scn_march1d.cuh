@@ -163,7 +163,10 @@ __global__ void __launch_bounds__(MARCH1D_BLOCK) k_cond1d(const __grid_constant_
 
 // VAR: 0 = stationary kernel, 1 = brute-force non-stationary (point-dependent kernel scale), 2 = multi-resolution (two levels, SCN:126-135)
 template <bool TRANSMIT, int NIMP, int VAR>
-__global__ void __launch_bounds__(MARCH1D_BLOCK) k_march1d(const __grid_constant__ Params P, const MarchArgs A, const Scratch1D X) {
+// resident blocks per SM the register allocation must allow: 5 (<= 102 registers) for stationary media, 4 / 3 for the brute-force and
+// multi-resolution variants; the calls into the procedural-field code (cold for most media) then spill around the call instead of
+// raising the whole kernel's register count
+__global__ void __launch_bounds__(MARCH1D_BLOCK, VAR == 0 ? 5 : (VAR == 1 ? 4 : 3)) k_march1d(const __grid_constant__ Params P, const MarchArgs A, const Scratch1D X) {
     const unsigned FULL = 0xffffffffu;
     const int lane = threadIdx.x & 31;
     const unsigned lt = (1u << lane) - 1u;
@@ -292,7 +295,7 @@ __global__ void __launch_bounds__(MARCH1D_BLOCK) k_march1d(const __grid_constant
             nv = MULTI ? nv + (l ? L.r_hi : L.r_lo) * nl : nl; // SCN:131-134
         }
         if (active) {
-            const float amp = cov_amplitude(P, p);
+            const float amp = VAR == 0 ? P.sigma : cov_amplitude(P, p); // stationary instantiations carry no procedural-field code
             double mean; gp_mean_and_id(P, p, mean, id);
             if (P.surf_vol_sep) id = 1.f < P.surf_vol_thresh ? 0 : 1;
             fval = (float)yadd((double)xmul(amp, nv), mean);
@@ -337,7 +340,7 @@ __global__ void __launch_bounds__(MARCH1D_BLOCK) k_march1d(const __grid_constant
                 if (A.n_evals) A.n_evals[ri] = evals + (hit ? 1u : 0u);
             } else {
                 uint32_t scheme = SCN_SCHEME_UNI;
-                if (hit) scheme = cov_amplitude(P, ray_at(o, rd, t_fin)) < 1e-6f ? SCN_SCHEME_UNI : (uint32_t)P.scheme; // samplingScheme (SCN:51-58)
+                if (hit) scheme = (VAR == 0 ? P.sigma : cov_amplitude(P, ray_at(o, rd, t_fin))) < 1e-6f ? SCN_SCHEME_UNI : (uint32_t)P.scheme; // samplingScheme (SCN:51-58)
                 const float th = (float)t_fin;
                 X.t_hi[ri] = th; X.t_lo[ri] = (float)(t_fin - (double)th); X.last_val[ri] = last_val;
                 X.flags[ri] = (hit ? 1u : 0u) | (scheme << 8); X.gp_id[ri] = gp_id;
