@@ -492,8 +492,33 @@ static void cov_kernel1d(const orc_medium *m, float pq, float pc, v3 pc_world, f
 static float cov_c1d_ls(const orc_medium *m, v3 pqw, v3 pcw) { return m->stationary ? 1.0f : cov_splat_cov1d(m, pqw, pcw); }
 
 /* ------------------------------------------------------------------ mean (GPF.hpp:867-1005, GaussianProcess.cpp:379-393) */
+/* ProceduralMean::mean (GPF:279-285) over SdfFunctions::eval (math/SdfFunctions.hpp:47-55, SdfFunctions.cpp:148-157, 181-183) or the scalar field "f" */
+static double proc_mean(const scn_mean_desc *md, d3 a) {
+    float px = (float)a.x, py = (float)a.y, pz = (float)a.z;
+    const float *T = md->inv_transform;
+    float x = T[0] * px + T[1] * py + T[2] * pz + T[3], y = T[4] * px + T[5] * py + T[6] * pz + T[7], z = T[8] * px + T[9] * py + T[10] * pz + T[11];
+    float m;
+    switch (md->sdf_func) {
+    case SCN_SDF_PLANE: m = y; break;
+    case SCN_SDF_TWO_SPHERES: {
+        float y1 = y - 10.f, y2 = y - -10.f;
+        float a1 = sqrtf(x * x + y1 * y1 + z * z) - 9.5f, a2 = sqrtf(x * x + y2 * y2 + z * z) - 9.5f;
+        m = a1 < a2 ? a1 : a2; break;
+    }
+    case SCN_SDF_KNOB_INNER: {
+        const float scale = 0.8f; float k = (float)(1. / scale);
+        float qx = x * k, qy = y * k, qz = z * k;
+        m = (sqrtf(qx * qx + qy * qy + qz * qz) - 0.75f) * scale; break;
+    }
+    default: { d3 q = {x, y, z}; m = (float)field_scalar(&md->f, q); break; }
+    }
+    m *= md->scale;
+    float r = m + md->offset;
+    return md->min > r ? md->min : r;
+}
 static double mean_eval(const scn_mean_desc *md, d3 a) {
     switch (md->type) {
+    case SCN_MEAN_PROCEDURAL: return proc_mean(md, a);
     case SCN_MEAN_HOMOGENEOUS: return md->offset;
     case SCN_MEAN_SPHERICAL: { d3 q = {a.x - md->center[0], a.y - md->center[1], a.z - md->center[2]}; return d3_len(q) - md->radius; }
     case SCN_MEAN_LINEAR: {
@@ -506,6 +531,12 @@ static double mean_eval(const scn_mean_desc *md, d3 a) {
 static d3 mean_grad(const scn_mean_desc *md, d3 a) {
     d3 r = {0., 0., 0.};
     switch (md->type) {
+    case SCN_MEAN_PROCEDURAL: { /* ProceduralMean::dmean_da (GPF:287-296) */
+        double eps = 0.001f;
+        d3 ax = a, ay = a, az = a; ax.x += eps; ay.y += eps; az.z += eps;
+        double v0 = proc_mean(md, a), v1 = proc_mean(md, ax), v2 = proc_mean(md, ay), v3 = proc_mean(md, az);
+        r.x = (v1 - v0) / eps; r.y = (v2 - v0) / eps; r.z = (v3 - v0) / eps; return r;
+    }
     case SCN_MEAN_SPHERICAL: { d3 q = {a.x - md->center[0], a.y - md->center[1], a.z - md->center[2]}; double inv = 1.0 / d3_len(q); r.x = q.x * inv; r.y = q.y * inv; r.z = q.z * inv; return r; }
     case SCN_MEAN_LINEAR: {
         d3 q = {a.x - md->ref[0], a.y - md->ref[1], a.z - md->ref[2]}, dir = {md->dir[0], md->dir[1], md->dir[2]};

@@ -186,7 +186,7 @@ struct scn_medium {
     bool march1d = false; // 1D-sampling media covered by k_march1d (scn_march1d.cuh)
     cudaMemPool_t pool = nullptr; // k_march1d's per-call scratch (stream-ordered allocations of this medium only)
     bool force_generic = false;   // scn_debug_force_generic: tests compare the tuned kernels with the one-thread-per-ray ones
-    double *grids[3] = {nullptr, nullptr, nullptr}; // device copies of the regular_grid fields ("ls", "var", "aniso")
+    double *grids[5] = {nullptr, nullptr, nullptr, nullptr, nullptr}; // device copies of the regular_grid fields ("ls", "var", "aniso", the two procedural means' "f")
 };
 
 static inline unsigned grid_for(size_t n) { return (unsigned)((n + BLOCK - 1) / BLOCK); }
@@ -242,15 +242,15 @@ int scn_medium_create(const scn_medium_desc *desc, int device, scn_medium **out)
         cudaError_t e2 = cudaMalloc((void **)&m->counters, scn_medium::COUNTERS * sizeof(unsigned int));
         if (e1 != cudaSuccess || e2 != cudaSuccess) { delete m; return cuda_fail(e1 != cudaSuccess ? e1 : e2, "scn_medium_create"); }
         // regular_grid fields: the descriptor's host arrays -> device memory owned by the medium (the kernels read them through Params)
-        FieldK *fk[3] = {&m->P.ls, &m->P.var, &m->P.aniso_f};
-        scn_field_desc *fd[3] = {&m->desc.ls, &m->desc.var, &m->desc.aniso_field};
-        for (int i = 0; i < 3; ++i) {
+        FieldK *fk[5] = {&m->P.ls, &m->P.var, &m->P.aniso_f, &m->P.mean_f, &m->P.mean_add_f};
+        scn_field_desc *fd[5] = {&m->desc.ls, &m->desc.var, &m->desc.aniso_field, &m->desc.mean.f, &m->desc.mean_additional.f};
+        for (int i = 0; i < 5; ++i) {
             fd[i]->grid.values = nullptr; fd[i]->grid.owned = 0; // the medium keeps no reference to the caller's arrays
             if (fk[i]->type != SCN_FIELD_REGULAR_GRID) { fk[i]->grid = nullptr; continue; }
             const size_t bytes = (size_t)fk[i]->gres * fk[i]->gres * fk[i]->gres * fk[i]->gcomp * sizeof(double);
             cudaError_t eg = cudaMalloc((void **)&m->grids[i], bytes);
             if (eg == cudaSuccess) eg = cudaMemcpy(m->grids[i], fk[i]->grid, bytes, cudaMemcpyHostToDevice);
-            if (eg != cudaSuccess) { for (int j = 0; j < 3; ++j) if (m->grids[j]) cudaFree(m->grids[j]); cudaFree(m->counters); delete m; return cuda_fail(eg, "scn_medium_create: regular_grid upload"); }
+            if (eg != cudaSuccess) { for (int j = 0; j < 5; ++j) if (m->grids[j]) cudaFree(m->grids[j]); cudaFree(m->counters); delete m; return cuda_fail(eg, "scn_medium_create: regular_grid upload"); }
             fk[i]->grid = m->grids[i];
         }
         if (m->march1d) { // k_march1d's per-call scratch: a pool of this medium's own that keeps freed blocks cached instead of returning them at every sync
@@ -273,7 +273,7 @@ void scn_medium_destroy(scn_medium *m) {
         for (int i = 0; i < 3; ++i) { if (m->arena[i]) cudaFree(m->arena[i]); if (m->streams[i]) cudaStreamDestroy(m->streams[i]);
                                       if (m->ev_in[i]) cudaEventDestroy(m->ev_in[i]); if (m->ev_k[i]) cudaEventDestroy(m->ev_k[i]); if (m->ev_out[i]) cudaEventDestroy(m->ev_out[i]); }
         if (m->counters) cudaFree(m->counters);
-        for (int i = 0; i < 3; ++i) if (m->grids[i]) cudaFree(m->grids[i]);
+        for (int i = 0; i < 5; ++i) if (m->grids[i]) cudaFree(m->grids[i]);
         if (m->pool) { cudaDeviceSynchronize(); cudaMemPoolDestroy(m->pool); }
     }
     delete m;

@@ -398,8 +398,33 @@ SCN_HD float se_c1d_grad2(float ab, float ls) { float den = 4.0f * ls * ls; floa
 SCN_HD float se_c1d_grad2_normal(float ab, float ls) { float den = 4.0f * ls * ls; return -2.0f / den * se_c1d_val(ab, ls); }
 
 // ---------------------------------------------------------------- mean (GPF.hpp:867-1005, GaussianProcess.cpp:379-393) in double
-SCN_HD double mean_eval(const scn_mean_desc &md, dbl3 a) {
+// ProceduralMean::mean (math/GPFunctions.cpp:279-285): the point goes to float, through the inverse config transform
+// (Mat4f::transformPoint, math/Mat4f.hpp:168-175), into the SDF function (math/SdfFunctions.cpp) or the scalar field; float scale / offset / floor.
+SCN_FN double proc_mean(const scn_mean_desc &md, const FieldK &f, dbl3 a) {
+    const float px = (float)a.x, py = (float)a.y, pz = (float)a.z;
+    const float *T = md.inv_transform;
+    const f3 p = F3(xadd(xadd(xadd(xmul(T[0], px), xmul(T[1], py)), xmul(T[2], pz)), T[3]), xadd(xadd(xadd(xmul(T[4], px), xmul(T[5], py)), xmul(T[6], pz)), T[7]),
+                    xadd(xadd(xadd(xmul(T[8], px), xmul(T[9], py)), xmul(T[10], pz)), T[11]));
+    float m;
+    switch (md.sdf_func) {
+    case SCN_SDF_PLANE: m = p.y; break;
+    case SCN_SDF_TWO_SPHERES: { // min(|p - (0, 10, 0)| - 9.5, |p - (0, -10, 0)| - 9.5)
+        const float a1 = xsub(xsqrt(xlensq(F3(p.x, xsub(p.y, 10.f), p.z))), 9.5f), a2 = xsub(xsqrt(xlensq(F3(p.x, xsub(p.y, -10.f), p.z))), 9.5f);
+        m = a1 < a2 ? a1 : a2; break;
+    }
+    case SCN_SDF_KNOB_INNER: { // p *= 1. / 0.8f (1.25f after the conversion to float); (|p| - 0.75) * 0.8f
+        const f3 q = xscale3(p, 1.25f);
+        m = xmul(xsub(xsqrt(xlensq(q)), 0.75f), 0.8f); break;
+    }
+    default: m = (float)field_scalar(f, to_dbl3(p)); break;
+    }
+    m = xmul(m, md.scale);
+    const float r = xadd(m, md.offset);
+    return (double)(md.min > r ? md.min : r);
+}
+SCN_HD double mean_eval(const scn_mean_desc &md, const FieldK &mf, dbl3 a) {
     switch (md.type) {
+    case SCN_MEAN_PROCEDURAL: return proc_mean(md, mf, a);
     case SCN_MEAN_HOMOGENEOUS: return (double)md.offset;
     case SCN_MEAN_SPHERICAL: {
         double qx = ysub(a.x, md.center[0]), qy = ysub(a.y, md.center[1]), qz = ysub(a.z, md.center[2]);
@@ -413,8 +438,14 @@ SCN_HD double mean_eval(const scn_mean_desc &md, dbl3 a) {
     default: return 0.;
     }
 }
-SCN_HD f3 mean_grad(const scn_mean_desc &md, dbl3 a) {
+SCN_HD f3 mean_grad(const scn_mean_desc &md, const FieldK &mf, dbl3 a) {
     switch (md.type) {
+    case SCN_MEAN_PROCEDURAL: { // ProceduralMean::dmean_da (math/GPFunctions.cpp:287-296): forward differences, eps = double(0.001f)
+        const double eps = (double)0.001f;
+        dbl3 ax = a, ay = a, az = a; ax.x = yadd(a.x, eps); ay.y = yadd(a.y, eps); az.z = yadd(a.z, eps);
+        const double v0 = proc_mean(md, mf, a), v1 = proc_mean(md, mf, ax), v2 = proc_mean(md, mf, ay), v3 = proc_mean(md, mf, az);
+        return F3((float)ydiv(ysub(v1, v0), eps), (float)ydiv(ysub(v2, v0), eps), (float)ydiv(ysub(v3, v0), eps));
+    }
     case SCN_MEAN_SPHERICAL: {
         double qx = ysub(a.x, md.center[0]), qy = ysub(a.y, md.center[1]), qz = ysub(a.z, md.center[2]);
         double inv = ydiv(1.0, ysqrt(yadd(yadd(ymul(qx, qx), ymul(qy, qy)), ymul(qz, qz))));
@@ -431,10 +462,10 @@ SCN_HD f3 mean_grad(const scn_mean_desc &md, dbl3 a) {
 }
 SCN_HD void gp_mean_and_id(const Params &P, f3 p, double &mean, int &id) {
     dbl3 a = to_dbl3(p);
-    mean = mean_eval(P.mean, a); id = P.gp_id;
-    if (P.has_mean_add) { double v = mean_eval(P.mean_add, a); if (v < mean) { mean = v; id = P.id_add; } }
+    mean = mean_eval(P.mean, P.mean_f, a); id = P.gp_id;
+    if (P.has_mean_add) { double v = mean_eval(P.mean_add, P.mean_add_f, a); if (v < mean) { mean = v; id = P.id_add; } }
 }
-SCN_HD f3 gp_mean_grad(const Params &P, f3 p, int id) { return id == P.gp_id ? mean_grad(P.mean, to_dbl3(p)) : mean_grad(P.mean_add, to_dbl3(p)); }
+SCN_HD f3 gp_mean_grad(const Params &P, f3 p, int id) { return id == P.gp_id ? mean_grad(P.mean, P.mean_f, to_dbl3(p)) : mean_grad(P.mean_add, P.mean_add_f, to_dbl3(p)); }
 
 // ---------------------------------------------------------------- seeds and multi-resolution levels
 SCN_HD uint32_t compute_seed(const Params &P, const Info &in) { // SCN:40-49

@@ -63,6 +63,7 @@ struct Params {
     // GP
     int32_t gp_id, has_mean_add, id_add, _pad;
     scn_mean_desc mean, mean_add;
+    FieldK mean_f, mean_add_f;  // procedural means: the scalar field "f" behind mean / mean_add (a regular_grid here points at device memory)
     FieldK ls, var;
     FieldK aniso_f;            // proc_nonstationary "aniso": rotation-anisotropy field (math/GPFunctions.cpp:1678-1690); has_aniso = field present
     int32_t has_aniso;

@@ -9,6 +9,7 @@
 #include <cstring>
 
 #include "scn_internal.h"
+#include <initializer_list>
 
 namespace scn {
 
@@ -76,7 +77,12 @@ int params_from_desc(const scn_medium_desc &d, Params &p) {
         if (d.cov_type == SCN_COV_MATERN && d.matern_v != 0.5f && d.matern_v != 1.5f && d.matern_v != 2.5f)
             return set_error(SCN_EINVAL, "Matern kernel only implemented for v = 0.5, 1.5, 2.5");
     }
-    if (d.mean.type < SCN_MEAN_HOMOGENEOUS || d.mean.type > SCN_MEAN_LINEAR) return set_error(SCN_EINVAL, "bad mean type");
+    if (d.mean.type < SCN_MEAN_HOMOGENEOUS || d.mean.type > SCN_MEAN_PROCEDURAL) return set_error(SCN_EINVAL, "bad mean type");
+    for (const scn_mean_desc *md : {&d.mean, &d.mean_additional}) {
+        if (md->type != SCN_MEAN_PROCEDURAL) continue;
+        if (md->sdf_func < SCN_SDF_FIELD || md->sdf_func > SCN_SDF_PLANE) return set_error(SCN_EINVAL, "procedural mean: bad sdf_func");
+        if (md->sdf_func == SCN_SDF_FIELD && md->f.type == SCN_FIELD_NONE) return set_error(SCN_EINVAL, "procedural mean: neither a function nor a field");
+    }
     if (!(d.impulse_density >= 0.f) || d.impulse_density > 4096.f) return set_error(SCN_EINVAL, "impulse_density out of range");
     if (d.min_step == 0) return set_error(SCN_EINVAL, "min_step must be positive");
     p.n_imp = (uint32_t)d.impulse_density; p.density = d.impulse_density; p.global_seed = d.seed;
@@ -186,6 +192,10 @@ int params_from_desc(const scn_medium_desc &d, Params &p) {
     }
     p.gp_id = d.gp_id; p.has_mean_add = d.has_mean_additional; p.id_add = d.id_additional;
     p.mean = d.mean; p.mean_add = d.mean_additional;
+    if (int rc = check_grid(d.mean.f, "mean.f")) return rc;
+    if (int rc = check_grid(d.mean_additional.f, "mean_additional.f")) return rc;
+    field_k(d.mean.f, p.mean_f); field_k(d.mean_additional.f, p.mean_add_f); p.mean_f.gcomp = p.mean_add_f.gcomp = 1;
+    p.mean.f.grid.values = nullptr; p.mean_add.f.grid.values = nullptr; // the kernels read the grids through mean_f / mean_add_f only
     return SCN_OK;
 }
 

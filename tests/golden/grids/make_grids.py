@@ -39,6 +39,10 @@ def main():
     write("ls6_quadratic", smooth(rng, 6, 3, 0.5, 3.0), -1.5, 1.5, "quadratic")   # Vec3d: the largest component is the lateral scale
     write("ls7_linear", smooth(rng, 7, 3, 0.45, 2.4), -1.7, 1.7, "linear")
     write("aniso4_point", smooth(rng, 4, 1, 0.1, 0.9)[..., 0], -1.5, 1.5, "point")
+    # a tabulated signed distance (ProceduralMean over a regular_grid "f"): a torus of radii (0.8, 0.3) in the xz plane, sampled at cell centres
+    res = 12; ax = -1.6 + 3.2 * (np.arange(res) + 0.5) / res
+    x, y, z = np.meshgrid(ax, ax, ax, indexing="ij")
+    write("torus12_sdf_linear", np.sqrt((np.sqrt(x * x + z * z) - 0.8) ** 2 + y * y) - 0.3, -1.6, 1.6, "linear")
 
 
 if __name__ == "__main__":

@@ -141,6 +141,16 @@ MEDIA = {
     "grid_ls_multires_iso": medium(correlation_context="renewal+", single_realization=False, covariance=_nonstat(True, ls=_grid("ls6_quadratic"))),
     "grid_ls_var_multires_1d": medium(correlation_context="renewal+", single_realization=False, covariance=_nonstat(True, ls=_grid("ls7_linear"), var=_grid("var5_quadratic")),
                                       **{"1D_sampling": True, "1D_sampling_scheme": "mis", "1D_gradient_correlationXY": True}),
+    # "procedural" means (math/GPFunctions.hpp:1049-1087, GPFunctions.cpp:250-296): SDF functions of math/SdfFunctions.cpp and scalar fields
+    # (a regular_grid "f" is a tabulated signed distance), config transform, finite-difference gradient
+    "proc_mean_plane_world": medium(isotropic_3D_sampling=False, mean={"type": "procedural", "func": "plane", "scale": 0.9, "offset": 0.05,
+                                                                       "transform": {"position": [0.1, 0.2, -0.1], "rotation": [20, -35, 30], "scale": [1.2, 0.8, 1.0]}}),
+    "proc_mean_two_spheres_iso": medium(correlation_context="renewal+", single_realization=False,
+                                        mean={"type": "procedural", "func": "two_spheres", "scale": 0.1, "transform": {"scale": [0.1, 0.1, 0.1], "position": [0, 0.05, 0]}}),
+    "proc_mean_knob_inner_1d": medium(correlation_context="renewal", single_realization=False, mean={"type": "procedural", "f": {"type": "sdf", "function": "knob_inner"}, "min": -0.3},
+                                      **{"1D_sampling": True}),
+    "proc_mean_grid_sdf_iso": medium(correlation_context="renewal+", single_realization=False,
+                                     mean={"type": "procedural", "f": _grid("torus12_sdf_linear"), "transform": {"rotation": [0, 0, 25]}}),
     "grid_aniso_var_world": medium(isotropic_3D_sampling=False, correlation_context="renewal", single_realization=False,
                                    covariance=_nonstat(False, aniso=_grid("aniso4_point"), var=_grid("var5_quadratic"))),
 }
@@ -519,7 +529,8 @@ def ref_gpu_medium_stats(reset=False):
 # ------------------------------------------------------------------------------------------------ large-sample query parity
 PARITY_MEDIA = ["c1_sphere_3d_none", "c3_1d_renewal", "c4_1d_renewalplus_xy_mis", "c5_multires_nonstat_renewalplus", "iso_3d_renewalplus_aniso",
                 "world_3d_renewalplus", "multires_world", "nonstat_bruteforce_iso", "nonstat_bruteforce_world_var", "nonstat_bruteforce_1d_renewalplus",
-                "multires_1d_xy", "multires_1d_renewal", "grid_var_bruteforce_iso", "grid_ls_multires_iso", "grid_ls_var_multires_1d"]
+                "multires_1d_xy", "multires_1d_renewal", "grid_var_bruteforce_iso", "grid_ls_multires_iso", "grid_ls_var_multires_1d",
+                "proc_mean_two_spheres_iso", "proc_mean_grid_sdf_iso", "proc_mean_knob_inner_1d"]
 
 
 def checker(medium_json):
