@@ -72,6 +72,8 @@ extern "C" {
 #define SCN_FIELD_LEFT_RIGHT 3
 #define SCN_FIELD_FRONT_BACK 4
 #define SCN_FIELD_BOTTOM_TOP_LEFT_RIGHT 5
+#define SCN_FIELD_SANDSTONE 7   /* "noise":"sandstone": three nested fbm over simplex noise (math/GPFunctions.cpp:70-77, 104-111; math/SdfFunctions.cpp:200-296) */
+#define SCN_FIELD_RUST 8        /* "noise":"rust" (math/GPFunctions.cpp:78-83, 112-117) */
 #define SCN_FIELD_REGULAR_GRID 6 /* "type":"regular_grid" (RegularGridScalar / RegularGridVector, math/GPFunctions.hpp:429-578) */
 
 /* RegularGrid<ElemType>::interp (math/GPFunctions.hpp:241-306; strings of grids/Grid.cpp:6-26) */

@@ -186,6 +186,7 @@ orc_medium *orc_medium_create(const scn_medium_desc *desc) {
     if (!m->stationary && desc->ls.type != SCN_FIELD_NONE) {
         const scn_field_desc *f = &desc->ls;
         if (f->type == SCN_FIELD_CONSTANT) { double v = f->val[0] > f->val[1] ? f->val[0] : f->val[1]; v = v > f->val[2] ? v : f->val[2]; m->ls_max = (float)v; }
+        else if (f->type == SCN_FIELD_SANDSTONE || f->type == SCN_FIELD_RUST) m->ls_max = 1.f; /* ProceduralNoiseVec::maxVal (GPF:131-137) */
         else if (f->type == SCN_FIELD_REGULAR_GRID) m->ls_max = 1.f; /* the reference's maxVal() of a grid field is 0 (GPF.hpp:474-477): multi-resolution form only, which never reads it */
         else if (f->type == SCN_FIELD_BOTTOM_TOP_LEFT_RIGHT) m->ls_max = (float)((f->max > f->min ? f->max : f->min) * (f->max2 > f->min2 ? f->max2 : f->min2));
         else m->ls_max = (float)(f->max > f->min ? f->max : f->min);
@@ -242,8 +243,61 @@ static double field_grid(const scn_grid_desc *g, int ncomp, d3 p, int c) {
     }
     return quadd(vx[0], vx[1], vx[2], u);
 }
+/* fbm fields: random3 / simplex3d / fbm (math/SdfFunctions.cpp:200-296), float arithmetic, sin in double */
+static void fbm_random3(float cx, float cy, float cz, float *r) {
+    float dt = cx * 17.0f + cy * 59.4f + cz * 15.0f;
+    float j = (float)(4096.0 * sin((double)dt));
+    double v = 512.0 * j; r[2] = (float)(v - floor(v));
+    j = (float)(j * .125);
+    v = 512.0 * j; r[0] = (float)(v - floor(v));
+    j = (float)(j * .125);
+    v = 512.0 * j; r[1] = (float)(v - floor(v));
+    r[0] -= 0.5f; r[1] -= 0.5f; r[2] -= 0.5f;
+}
+static float dot3f(const float *a, const float *b) { float s = a[0] * b[0]; s += a[1] * b[1]; s += a[2] * b[2]; return s; }
+static float fbm_simplex3d(float px, float py, float pz) {
+    const float F3c = 0.3333333f, G3c = 0.1666667f;
+    float p[3] = {px, py, pz}, k3[3] = {F3c, F3c, F3c}, g3[3] = {G3c, G3c, G3c};
+    float ds = dot3f(p, k3), s[3], x[3], e[3], i1[3], i2[3], x1[3], x2[3], x3[3], w[4], d[4], r[3], q[3];
+    for (int i = 0; i < 3; ++i) s[i] = floorf(p[i] + ds);
+    float dg = dot3f(s, g3);
+    for (int i = 0; i < 3; ++i) x[i] = p[i] - s[i] + dg;
+    for (int i = 0; i < 3; ++i) e[i] = (x[i] - x[(i + 1) % 3]) < 0.0f ? 0.f : 1.f;
+    for (int i = 0; i < 3; ++i) { i1[i] = e[i] * (1.0f - e[(i + 2) % 3]); i2[i] = 1.0f - e[(i + 2) % 3] * (1.0f - e[i]); }
+    for (int i = 0; i < 3; ++i) { x1[i] = x[i] - i1[i] + G3c; x2[i] = x[i] - i2[i] + 2.0f * G3c; x3[i] = x[i] - 1.0f + 3.0f * G3c; }
+    w[0] = dot3f(x, x); w[1] = dot3f(x1, x1); w[2] = dot3f(x2, x2); w[3] = dot3f(x3, x3);
+    for (int i = 0; i < 4; ++i) { float t = 0.6f - w[i]; w[i] = t > 0.0f ? t : 0.0f; }
+    fbm_random3(s[0], s[1], s[2], r); d[0] = dot3f(r, x);
+    for (int i = 0; i < 3; ++i) q[i] = s[i] + i1[i]; fbm_random3(q[0], q[1], q[2], r); d[1] = dot3f(r, x1);
+    for (int i = 0; i < 3; ++i) q[i] = s[i] + i2[i]; fbm_random3(q[0], q[1], q[2], r); d[2] = dot3f(r, x2);
+    for (int i = 0; i < 3; ++i) q[i] = s[i] + 1.0f; fbm_random3(q[0], q[1], q[2], r); d[3] = dot3f(r, x3);
+    for (int i = 0; i < 4; ++i) { w[i] *= w[i]; w[i] *= w[i]; d[i] *= w[i]; }
+    float sum = d[0] * 52.0f; sum += d[1] * 52.0f; sum += d[2] * 52.0f; sum += d[3] * 52.0f;
+    return sum;
+}
+static double fbm_noise(d3 uv, int octaves) {
+    float gain = 0.65f, lacunarity = 2.1042f, total, frequency = 0.5f, amplitude = gain;
+    uv.x *= 5.0; uv.y *= 5.0; uv.z *= 5.0;
+    float qx = (float)uv.x, qy = (float)uv.y, qz = (float)uv.z;
+    total = fbm_simplex3d(qx, qy, qz);
+    for (int i = 0; i < octaves; ++i) { total += fbm_simplex3d(qx * frequency, qy * frequency, qz * frequency) * amplitude; frequency *= lacunarity; amplitude *= gain; }
+    total = (float)((total + 2.0) / 4.0);
+    return total;
+}
+static d3 d3_adds(d3 a, double s) { d3 r = {a.x + s, a.y + s, a.z + s}; return r; }
+static d3 d3_muls(d3 a, double s) { d3 r = {a.x * s, a.y * s, a.z * s}; return r; }
+static double fbm_sandstone(d3 p, int oct) { d3 ps = d3_muls(p, 0.3); return fbm_noise(d3_adds(ps, fbm_noise(d3_adds(ps, fbm_noise(ps, oct)), oct)), oct); }
+static double fbm_rust(d3 p, int oct, int plus) { /* GPF:78-83 (scalar: minus), 112-117 (vector: plus); smoothStep: math/MathUtil.hpp:108-112 */
+    d3 ps = d3_muls(p, 2.0);
+    double a = fbm_noise(d3_muls(ps, .1), oct) * 0.4, b = fbm_noise(d3_muls(ps, 25.), oct) * 0.1;
+    double v = plus ? fbm_noise(d3_adds(ps, a), oct) + b : fbm_noise(d3_adds(ps, a), oct) - b;
+    double x = clampd((v - 0.4) / (0.6 - 0.4), 0., 1.);
+    return x * x * (3.0 - 2.0 * x);
+}
 static double field_scalar(const scn_field_desc *f, d3 p) {
     switch (f->type) {
+    case SCN_FIELD_SANDSTONE: { double v = fbm_sandstone(p, 2); double cx = sqrt(v * 1.9 * 1.2) - 0.35; return lerpd(f->min, f->max, clampd(cx, 0., 1.)); } /* GPF:70-77 */
+    case SCN_FIELD_RUST: return lerpd(f->min, f->max, clampd(fbm_rust(p, 2, 0), 0., 1.));
     case SCN_FIELD_REGULAR_GRID: return field_grid(&f->grid, 1, p, 0); /* RegularGridScalar (GPF.hpp:429-437) */
     case SCN_FIELD_CONSTANT: return f->val[0];
     case SCN_FIELD_BOTTOM_TOP: case SCN_FIELD_LEFT_RIGHT: case SCN_FIELD_FRONT_BACK: return field_ramp(f, p, 0) - 1.;
@@ -254,6 +308,11 @@ static double field_scalar(const scn_field_desc *f, d3 p) {
 static d3 field_vector(const scn_field_desc *f, d3 p) {
     d3 r;
     if (f->type == SCN_FIELD_CONSTANT) { r.x = f->val[0]; r.y = f->val[1]; r.z = f->val[2]; return r; }
+    if (f->type == SCN_FIELD_SANDSTONE) { /* GPF:104-111 */
+        double v = fbm_sandstone(p, 10);
+        r.x = clampd((sqrt(v * 1.9 * 1.2) - 0.35) * 0.2, 0., 1.); r.y = clampd((sqrt(v * 0.7 * 1.2) - 0.35) * 0.2, 0., 1.); r.z = clampd((sqrt(v * 0.25 * 1.2) - 0.35) * 0.2, 0., 1.); return r;
+    }
+    if (f->type == SCN_FIELD_RUST) { double v = fbm_rust(p, 10, 1); r.x = lerpd(0.278, 1., v); r.y = lerpd(0.212, 1., v); r.z = lerpd(0.141, 1., v); return r; } /* GPF:112-117 */
     if (f->type == SCN_FIELD_REGULAR_GRID) { r.x = field_grid(&f->grid, 3, p, 0); r.y = field_grid(&f->grid, 3, p, 1); r.z = field_grid(&f->grid, 3, p, 2); return r; } /* RegularGridVector (GPF.hpp:504-512) */
     double v = field_scalar(f, p); r.x = r.y = r.z = v; return r;
 }

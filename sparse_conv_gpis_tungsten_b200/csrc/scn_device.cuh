@@ -169,8 +169,75 @@ SCN_FN double field_grid(const FieldK &k, dbl3 p, int c) {
     }
     return quad_d(vx[0], vx[1], vx[2], u);
 }
+// ---- fbm fields (math/SdfFunctions.cpp:200-296): simplex noise over a sin() hash.  Float arithmetic in the reference's order; the hash
+// takes sin in DOUBLE of the float dot product and rounds 4096 sin(.) to float (random3, :201-210), which the device's double sin
+// reproduces (both are within an ulp of the exact value; the rounding to float hides that except ~1e-8 of the time).
+SCN_HD f3 fbm_random3(f3 c) {
+    const float dt = xadd(xadd(xmul(c.x, 17.0f), xmul(c.y, 59.4f)), xmul(c.z, 15.0f));
+    float j = (float)ymul(4096.0, sin((double)dt));
+    f3 r;
+    double v = ymul(512.0, (double)j); r.z = (float)ysub(v, floor(v));
+    j = (float)ymul((double)j, .125);
+    v = ymul(512.0, (double)j); r.x = (float)ysub(v, floor(v));
+    j = (float)ymul((double)j, .125);
+    v = ymul(512.0, (double)j); r.y = (float)ysub(v, floor(v));
+    return F3(xsub(r.x, 0.5f), xsub(r.y, 0.5f), xsub(r.z, 0.5f));
+}
+SCN_FN float fbm_simplex3d(f3 p) {
+    const float F3c = 0.3333333f, G3c = 0.1666667f;
+    const float ds = xadd(xadd(xmul(p.x, F3c), xmul(p.y, F3c)), xmul(p.z, F3c));
+    const f3 s = F3(floorf(xadd(p.x, ds)), floorf(xadd(p.y, ds)), floorf(xadd(p.z, ds)));
+    const float dg = xadd(xadd(xmul(s.x, G3c), xmul(s.y, G3c)), xmul(s.z, G3c));
+    const f3 x = F3(xadd(xsub(p.x, s.x), dg), xadd(xsub(p.y, s.y), dg), xadd(xsub(p.z, s.z), dg));
+    const f3 e = F3(xsub(x.x, x.y) < 0.f ? 0.f : 1.f, xsub(x.y, x.z) < 0.f ? 0.f : 1.f, xsub(x.z, x.x) < 0.f ? 0.f : 1.f);
+    const f3 i1 = F3(xmul(e.x, xsub(1.0f, e.z)), xmul(e.y, xsub(1.0f, e.x)), xmul(e.z, xsub(1.0f, e.y)));
+    const f3 i2 = F3(xsub(1.0f, xmul(e.z, xsub(1.0f, e.x))), xsub(1.0f, xmul(e.x, xsub(1.0f, e.y))), xsub(1.0f, xmul(e.y, xsub(1.0f, e.z))));
+    const float g2 = xmul(2.0f, G3c), g3 = xmul(3.0f, G3c);
+    const f3 x1 = F3(xadd(xsub(x.x, i1.x), G3c), xadd(xsub(x.y, i1.y), G3c), xadd(xsub(x.z, i1.z), G3c));
+    const f3 x2 = F3(xadd(xsub(x.x, i2.x), g2), xadd(xsub(x.y, i2.y), g2), xadd(xsub(x.z, i2.z), g2));
+    const f3 x3 = F3(xadd(xsub(x.x, 1.0f), g3), xadd(xsub(x.y, 1.0f), g3), xadd(xsub(x.z, 1.0f), g3));
+    float w0 = xsub(0.6f, xdot(x, x)), w1 = xsub(0.6f, xdot(x1, x1)), w2 = xsub(0.6f, xdot(x2, x2)), w3 = xsub(0.6f, xdot(x3, x3));
+    w0 = w0 > 0.f ? w0 : 0.f; w1 = w1 > 0.f ? w1 : 0.f; w2 = w2 > 0.f ? w2 : 0.f; w3 = w3 > 0.f ? w3 : 0.f;
+    float d0 = xdot(fbm_random3(s), x), d1 = xdot(fbm_random3(F3(xadd(s.x, i1.x), xadd(s.y, i1.y), xadd(s.z, i1.z))), x1),
+          d2 = xdot(fbm_random3(F3(xadd(s.x, i2.x), xadd(s.y, i2.y), xadd(s.z, i2.z))), x2), d3 = xdot(fbm_random3(F3(xadd(s.x, 1.0f), xadd(s.y, 1.0f), xadd(s.z, 1.0f))), x3);
+    w0 = xmul(w0, w0); w1 = xmul(w1, w1); w2 = xmul(w2, w2); w3 = xmul(w3, w3);
+    w0 = xmul(w0, w0); w1 = xmul(w1, w1); w2 = xmul(w2, w2); w3 = xmul(w3, w3);
+    d0 = xmul(d0, w0); d1 = xmul(d1, w1); d2 = xmul(d2, w2); d3 = xmul(d3, w3);
+    return xadd(xadd(xadd(xmul(d0, 52.0f), xmul(d1, 52.0f)), xmul(d2, 52.0f)), xmul(d3, 52.0f));
+}
+SCN_FN double fbm_noise(dbl3 uv, int octaves) { // fbm (math/SdfFunctions.cpp:276-296)
+    const float gain = 0.65f, lacunarity = 2.1042f;
+    float frequency = 0.5f, amplitude = gain;
+    uv.x = ymul(uv.x, 5.0); uv.y = ymul(uv.y, 5.0); uv.z = ymul(uv.z, 5.0);
+    const f3 q = F3((float)uv.x, (float)uv.y, (float)uv.z);
+    float total = fbm_simplex3d(q);
+    for (int i = 0; i < octaves; ++i) {
+        total = xadd(total, xmul(fbm_simplex3d(xscale3(q, frequency)), amplitude));
+        frequency = xmul(frequency, lacunarity); amplitude = xmul(amplitude, gain);
+    }
+    total = (float)ydiv(yadd((double)total, 2.0), 4.0);
+    return (double)total;
+}
+SCN_HD dbl3 dadd_s(dbl3 a, double s) { dbl3 r; r.x = yadd(a.x, s); r.y = yadd(a.y, s); r.z = yadd(a.z, s); return r; }
+SCN_HD dbl3 dmul_s(dbl3 a, double s) { dbl3 r; r.x = ymul(a.x, s); r.y = ymul(a.y, s); r.z = ymul(a.z, s); return r; }
+SCN_HD double clamp01_d(double v) { const double t = v > 0. ? v : 0.; return t < 1. ? t : 1.; } // min(max(v, 0), 1) with Tungsten's a > b ? a : b
+// the fbm value both Sandstone branches share (GPF:72-73 with 2 octaves, :106-107 with 10), and Rust's smoothStep argument (:80, :114)
+SCN_FN double fbm_sandstone(dbl3 p, int oct) { const dbl3 ps = dmul_s(p, 0.3); return fbm_noise(dadd_s(ps, fbm_noise(dadd_s(ps, fbm_noise(ps, oct)), oct)), oct); }
+SCN_FN double fbm_rust(dbl3 p, int oct, double sign) {
+    const dbl3 ps = dmul_s(p, 2.0);
+    const double a = ymul(fbm_noise(dmul_s(ps, .1), oct), 0.4), b = ymul(fbm_noise(dmul_s(ps, 25.), oct), 0.1);
+    const double v = yadd(fbm_noise(dadd_s(ps, a), oct), sign > 0 ? b : -b); // scalar field: minus (GPF:80); vector field: plus (GPF:114)
+    const double x = clamp01_d(ydiv(ysub(v, 0.4), ysub(0.6, 0.4)));
+    return ymul(ymul(x, x), ysub(3.0, ymul(2.0, x))); // smoothStep (math/MathUtil.hpp:108-112)
+}
 SCN_FN double field_scalar(const FieldK &k, dbl3 p) {
     switch (k.type) {
+    case SCN_FIELD_SANDSTONE: { // ProceduralNoise::operator() (GPF:70-77)
+        const double f = fbm_sandstone(p, 2);
+        const double cx = ysub(sqrt(ymul(ymul(f, 1.9), 1.2)), 0.35), t = clamp01_d(cx);
+        return yadd(ymul(k.fmin, ysub(1.0, t)), ymul(k.fmax, t));
+    }
+    case SCN_FIELD_RUST: { const double t = clamp01_d(fbm_rust(p, 2, -1.0)); return yadd(ymul(k.fmin, ysub(1.0, t)), ymul(k.fmax, t)); } // GPF:78-83
     case SCN_FIELD_REGULAR_GRID: return field_grid(k, p, 0);
     case SCN_FIELD_CONSTANT: return k.val[0];
     case SCN_FIELD_BOTTOM_TOP: return field_ramp(k, p.y, 0) - 1.;
@@ -186,6 +253,16 @@ SCN_HD dbl3 to_dbl3(f3 p) { dbl3 r; r.x = p.x; r.y = p.y; r.z = p.z; return r; }
 SCN_HD float cov_lateral_scale(const Params &P, f3 p) { // sparseConvNoiseLateralScale
     if (P.stationary || P.ls.type == SCN_FIELD_NONE) return 1.0f;
     if (P.ls.type == SCN_FIELD_CONSTANT) return max3((float)P.ls.val[0], (float)P.ls.val[1], (float)P.ls.val[2]);
+    if (P.ls.type == SCN_FIELD_SANDSTONE) { // ProceduralNoiseVec::operator() (GPF:104-111): clamp(col * 0.2, 0, 1), 10 octaves; largest component
+        const double f = fbm_sandstone(to_dbl3(p), 10);
+        const double c0 = clamp01_d(ymul(ysub(sqrt(ymul(ymul(f, 1.9), 1.2)), 0.35), 0.2)), c1 = clamp01_d(ymul(ysub(sqrt(ymul(ymul(f, 0.7), 1.2)), 0.35), 0.2)),
+                     c2 = clamp01_d(ymul(ysub(sqrt(ymul(ymul(f, 0.25), 1.2)), 0.35), 0.2));
+        return max3((float)c0, (float)c1, (float)c2);
+    }
+    if (P.ls.type == SCN_FIELD_RUST) { // GPF:112-117: lerp((0.278, 0.212, 0.141), 1, f)
+        const double f = fbm_rust(to_dbl3(p), 10, 1.0), g = ysub(1.0, f);
+        return max3((float)yadd(ymul(0.278, g), ymul(1.0, f)), (float)yadd(ymul(0.212, g), ymul(1.0, f)), (float)yadd(ymul(0.141, g), ymul(1.0, f)));
+    }
     if (P.ls.type == SCN_FIELD_REGULAR_GRID) { // getKernelScale (GPF:1729-1735): Vec3f of the interpolated Vec3d, largest component
         const dbl3 q = to_dbl3(p);
         return max3((float)field_grid(P.ls, q, 0), (float)field_grid(P.ls, q, 1), (float)field_grid(P.ls, q, 2));

@@ -29,6 +29,7 @@ struct FieldK {
     // regular_grid (math/GPFunctions.hpp:241-330): res^3 x ncomp doubles — device memory inside the kernels, the caller's host array in
     // params_from_desc and in tests/hostsim; bounds and the diagonal as the reference's getValue reads them
     const double *grid; double gmin[3], gdiag[3]; int32_t gres, ginterp, gcomp, _pad2;
+    double fmin, fmax; // sandstone / rust scalar fields: "min" / "max" as given (lerp end points)
 };
 
 // Everything a kernel needs, derived once from scn_medium_desc in scn_medium_create (device copy lives in

@@ -184,7 +184,8 @@ int parseField(const JVal &j, scn_field_desc &f, bool vector) {
     else if (noise == "left_right") f.type = SCN_FIELD_LEFT_RIGHT;
     else if (noise == "front_back") f.type = SCN_FIELD_FRONT_BACK;
     else if (noise == "bottom_top_left_right") f.type = SCN_FIELD_BOTTOM_TOP_LEFT_RIGHT;
-    else if (noise == "sandstone" || noise == "rust") return set_error(SCN_EUNSUPPORTED, "noise field '%s' (fbm) is not covered", noise.c_str());
+    else if (noise == "sandstone") f.type = SCN_FIELD_SANDSTONE;
+    else if (noise == "rust") f.type = SCN_FIELD_RUST;
     else return set_error(SCN_EJSON, "Invalid noise typ function: '%s'", noise.c_str());
     getD(j, "min", f.min); getD(j, "max", f.max); getD(j, "start", f.start); getD(j, "end", f.end);
     getD(j, "min2", f.min2); getD(j, "max2", f.max2); getD(j, "start2", f.start2); getD(j, "end2", f.end2);

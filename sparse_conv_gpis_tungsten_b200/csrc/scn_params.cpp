@@ -47,6 +47,7 @@ static void field_k(const scn_field_desc &f, FieldK &k) {
     double mn = f.min + c, mx = f.max + c, mn2 = f.min2 + c, mx2 = f.max2 + c;
     k.la[0] = std::log(mn * mn); k.lb[0] = std::log(mx * mx); k.scale[0] = 1.0 / (f.end - f.start); k.off[0] = -f.start * k.scale[0];
     k.la[1] = std::log(mn2 * mn2); k.lb[1] = std::log(mx2 * mx2); k.scale[1] = 1.0 / (f.end2 - f.start2); k.off[1] = -f.start2 * k.scale[1];
+    k.fmin = f.min; k.fmax = f.max;
     if (f.type == SCN_FIELD_REGULAR_GRID) { // Box3d::diagonal() = max - min (math/Box.hpp:62-65)
         k.grid = f.grid.values; k.gres = (int32_t)f.grid.res; k.ginterp = f.grid.interp;
         for (int i = 0; i < 3; ++i) { k.gmin[i] = f.grid.bounds_min[i]; k.gdiag[i] = f.grid.bounds_max[i] - f.grid.bounds_min[i]; }
@@ -126,6 +127,7 @@ int params_from_desc(const scn_medium_desc &d, Params &p) {
         const scn_field_desc &f = d.ls;
         if (f.type == SCN_FIELD_CONSTANT) p.ls_max = (float)std::fmax(std::fmax(f.val[0], f.val[1]), f.val[2]);
         else if (f.type == SCN_FIELD_BOTTOM_TOP_LEFT_RIGHT) p.ls_max = (float)(std::fmax(f.max, f.min) * std::fmax(f.max2, f.min2));
+        else if (f.type == SCN_FIELD_SANDSTONE || f.type == SCN_FIELD_RUST) p.ls_max = 1.f; // ProceduralNoiseVec::maxVal (GPF:131-137)
         else if (f.type == SCN_FIELD_REGULAR_GRID) p.ls_max = 1.f; // accepted in the multi-resolution form only (below), which never reads it
         else p.ls_max = (float)std::fmax(f.max, f.min);
     }

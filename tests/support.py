@@ -151,6 +151,14 @@ MEDIA = {
                                       **{"1D_sampling": True}),
     "proc_mean_grid_sdf_iso": medium(correlation_context="renewal+", single_realization=False,
                                      mean={"type": "procedural", "f": _grid("torus12_sdf_linear"), "transform": {"rotation": [0, 0, 25]}}),
+    # fbm fields "sandstone" / "rust" (math/GPFunctions.cpp:70-83, 104-117 over math/SdfFunctions.cpp:200-296: simplex noise on a sin() hash)
+    "fbm_sandstone_var_bruteforce_iso": medium(correlation_context="renewal+", single_realization=False,
+                                               covariance=_nonstat(False, var={"type": "noise", "noise": "sandstone", "min": 0.6, "max": 1.8})),
+    "fbm_rust_var_world": medium(isotropic_3D_sampling=False, correlation_context="global", single_realization=False,
+                                 covariance=_nonstat(False, var={"type": "noise", "noise": "rust", "min": 0.5, "max": 2.0})),
+    "fbm_rust_ls_multires_iso": medium(correlation_context="renewal+", single_realization=False, covariance=_nonstat(True, ls={"type": "noise", "noise": "rust"})),
+    "fbm_rust_ls_bruteforce_1d": medium(correlation_context="renewal", single_realization=False, covariance=_nonstat(False, ls={"type": "noise", "noise": "rust"}),
+                                        **{"1D_sampling": True}),
     "grid_aniso_var_world": medium(isotropic_3D_sampling=False, correlation_context="renewal", single_realization=False,
                                    covariance=_nonstat(False, aniso=_grid("aniso4_point"), var=_grid("var5_quadratic"))),
 }

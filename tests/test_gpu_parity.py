@@ -171,8 +171,12 @@ def test_march_round_trip_properties(torch_cuda):
 # Bounds of the large-sample query parity, per (medium, wavefront): (decision, step_moved, t_rel_max, grad_rel_max, ctx_rel_max).
 # Integers are (observed on B200 + 1), relative errors the observed maximum rounded up; every number is in
 # profiles/r02_parity_rates.txt (tools/parity_rates.py).  north_star's tolerance is 1e-4: entries above it are explained there.
-DEFAULT_BOUND = (3, 3, 1e-4, 3e-4, 1e-3)
-PARITY_BOUNDS = {}
+DEFAULT_BOUND = (3, 3, 1e-4, 3e-4, 1e-3, TOL)  # last: 99.9 % quantile of the gradient error
+# A ProceduralMean's gradient is a forward difference with eps = 1e-3 of a mean held in FLOAT (math/GPFunctions.cpp:279-296): the
+# reference's own gradient carries ulp(mean) / eps ~ 1e-4 ... 3e-3 of rounding noise, re-drawn whenever the hit point moves by an ulp.
+# The mean itself is bit-identical (golden media); the bound below is that noise, measured (profiles/r02_parity_rates.txt).
+_FD = (3, 3, 1e-4, 5e-3, 1e-3, 5e-4)
+PARITY_BOUNDS = {(n, sec): _FD for n in ("proc_mean_two_spheres_iso", "proc_mean_grid_sdf_iso", "proc_mean_knob_inner_1d") for sec in (False, True)}
 
 
 @pytest.mark.parametrize("secondary", [False, True])
@@ -186,10 +190,10 @@ def test_march_kernels_vs_reference_8k_rays(torch_cuda, name, secondary):
     r = S.query_parity_case(name, secondary)
     if S.have_ref():
         assert r["checker"] == "ref"
-    dec, moved, t_max, g_max, c_max = PARITY_BOUNDS.get((name, secondary), DEFAULT_BOUND)
+    dec, moved, t_max, g_max, c_max, g_p999 = PARITY_BOUNDS.get((name, secondary), DEFAULT_BOUND)
     assert r["decision"] <= dec and r["step_moved"] <= moved, r
     assert r["t_rel_max"] <= t_max, r
-    assert r["grad_rel_p999"] <= TOL and r["grad_rel_max"] <= g_max, r
+    assert r["grad_rel_p999"] <= g_p999 and r["grad_rel_max"] <= g_max, r
     assert max(r["ctx_rel_p999"]) <= TOL and max(r["ctx_rel_max"]) <= c_max, r
     assert r["state_int_mismatch"] == 0 and r["scheme_mismatch"] == 0, r
     assert r["transmittance_mismatch"] <= 2, r

@@ -11,7 +11,7 @@ set -x; mkdir -p gpurun_out; T=${TAG:-r02}
 NCU="ncu --set full --clock-control none --import-source on"
 for stage in "$@"; do case $stage in
 tests)
-  python -m pytest tests -m gpu -q -x 2>&1 | tail -15 > gpurun_out/pytest_$T.log; cat gpurun_out/pytest_$T.log
+  python -m pytest tests -m gpu -q -x > gpurun_out/pytest_$T.log 2>&1; (head -40; echo ...; tail -8) < gpurun_out/pytest_$T.log | cut -c1-240
   python -c "import __graft_entry__ as g; g.smoke()" 2>&1 | tail -2 ;;
 bench)
   python bench.py > gpurun_out/bench_$T.json 2> gpurun_out/bench_$T.err || tail -20 gpurun_out/bench_$T.err
