@@ -281,6 +281,9 @@ def run_gpu(args):
                 qs = float(np.median(times))
                 tq = torch.tensor([qs], device=dev, dtype=torch.float64)
                 if world > 1:
+                    allq = [torch.zeros_like(tq) for _ in range(world)]
+                    dist.all_gather(allq, tq)
+                    row[("secondary" if secondary else "primary") + "_per_rank_ms"] = [round(float(t_.item()) * 1e3, 3) for t_ in allq]
                     dist.all_reduce(tq, op=dist.ReduceOp.MAX)
                 qs = float(tq.item())
                 ev = int(out["n_evals"].view(torch.int32).to(torch.int64).sum().item())
@@ -334,11 +337,16 @@ def run_gpu(args):
             a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             a.record(stream); wr.render(spp); img = R.gather_image_rgb(wr, world); b.record(stream); torch.cuda.synchronize()
             tr = torch.tensor([a.elapsed_time(b)], device=dev, dtype=torch.float64)
-            if world > 1:
+            per_rank = [float(tr.item())]
+            if world > 1:  # every rank's own time (the render is as slow as its slowest rank: load balance and per-GPU speed are both in here)
+                allt = [torch.zeros_like(tr) for _ in range(world)]
+                dist.all_gather(allt, tr)
+                per_rank = [float(t_.item()) for t_ in allt]
                 dist.all_reduce(tr, op=dist.ReduceOp.MAX)
             res = sc["camera"]["resolution"]
             out = {"workload": "%s %dx%d @%dspp, max_bounces %d, nee %s, 16x16 tiles over %d GPU(s) (%s), one all_gather" % (label, res[0], res[1], spp, sc["integrator"]["max_bounces"], "on" if wr.nee else "off", world, wr.sharding),
-                   "ms": float(tr.item()), "camera_paths": res[0] * res[1] * spp, "camera_paths_per_s": res[0] * res[1] * spp / (float(tr.item()) * 1e-3), "mean_radiance": float(img.mean().item())}
+                   "ms": float(tr.item()), "camera_paths": res[0] * res[1] * spp, "camera_paths_per_s": res[0] * res[1] * spp / (float(tr.item()) * 1e-3), "mean_radiance": float(img.mean().item()),
+                   "per_rank_ms": [round(v, 3) for v in per_rank]}
             wr.close()
             return out
 

@@ -50,7 +50,8 @@ struct ScnApi {
     void *handle = nullptr;
     int device = 0;
     decltype(&scn_last_error) last_error = nullptr;
-    decltype(&scn_desc_from_json) desc_from_json = nullptr;
+    decltype(&scn_desc_from_json_at) desc_from_json_at = nullptr;
+    decltype(&scn_desc_release) desc_release = nullptr;
     decltype(&scn_medium_create) medium_create = nullptr;
     decltype(&scn_medium_destroy) medium_destroy = nullptr;
     decltype(&scn_sample_distance_batch_host) sample_distance_host = nullptr;
@@ -70,7 +71,7 @@ namespace Tungsten {
 
 class GpuSparseConvolutionNoiseMedium : public SparseConvolutionNoiseMedium
 {
-    std::string _json;
+    std::string _json, _dir;
     scn_medium *_h[HANDLES] = {};
 
     scn_medium *handle() const
@@ -105,8 +106,9 @@ public:
         SparseConvolutionNoiseMedium::fromJson(value, scene);
         rapidjson::StringBuffer sb;
         rapidjson::Writer<rapidjson::StringBuffer> w(sb);
-        value._value->Accept(w); // the medium's JSON object, handed to scn_desc_from_json unchanged
+        value._value->Accept(w); // the medium's JSON object, handed to scn_desc_from_json_at unchanged
         _json = sb.GetString();
+        _dir = scene.path().parent().absolute().asString(); // relative resources ("file" of a regular_grid field) resolve like Scene::fetchResource
     }
 
     void prepareForRender() override
@@ -115,9 +117,10 @@ public:
         if (!g_api.handle) FAIL("sparse_conv_noise_gpu: libscn_b200.so is not loaded (ref_gpu_medium_register)");
         release();
         scn_medium_desc d;
-        if (g_api.desc_from_json(_json.c_str(), &d) != SCN_OK) FAIL("sparse_conv_noise_gpu: %s", g_api.last_error());
+        if (g_api.desc_from_json_at(_json.c_str(), _dir.empty() ? nullptr : _dir.c_str(), &d) != SCN_OK) FAIL("sparse_conv_noise_gpu: %s", g_api.last_error());
         for (int i = 0; i < HANDLES; ++i)
-            if (g_api.medium_create(&d, g_api.device, &_h[i]) != SCN_OK) FAIL("sparse_conv_noise_gpu: %s", g_api.last_error());
+            if (g_api.medium_create(&d, g_api.device, &_h[i]) != SCN_OK) { g_api.desc_release(&d); FAIL("sparse_conv_noise_gpu: %s", g_api.last_error()); }
+        g_api.desc_release(&d); // grids read from disk: every medium holds its own device copy
         g_n_media++;
     }
 
@@ -239,7 +242,7 @@ int ref_gpu_medium_register(const char *libscn_path, int device)
         if (!h) { g_shim_err = std::string("dlopen failed: ") + dlerror(); return -1; }
         ScnApi a; a.handle = h; a.device = device;
 #define SCN_SYM(field, name) a.field = (decltype(a.field))dlsym(h, #name); if (!a.field) { g_shim_err = "missing symbol " #name; dlclose(h); return -1; }
-        SCN_SYM(last_error, scn_last_error) SCN_SYM(desc_from_json, scn_desc_from_json) SCN_SYM(medium_create, scn_medium_create)
+        SCN_SYM(last_error, scn_last_error) SCN_SYM(desc_from_json_at, scn_desc_from_json_at) SCN_SYM(desc_release, scn_desc_release) SCN_SYM(medium_create, scn_medium_create)
         SCN_SYM(medium_destroy, scn_medium_destroy) SCN_SYM(sample_distance_host, scn_sample_distance_batch_host)
         SCN_SYM(transmittance_host, scn_transmittance_batch_host)
 #undef SCN_SYM

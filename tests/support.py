@@ -538,7 +538,8 @@ def ref_gpu_medium_stats(reset=False):
 PARITY_MEDIA = ["c1_sphere_3d_none", "c3_1d_renewal", "c4_1d_renewalplus_xy_mis", "c5_multires_nonstat_renewalplus", "iso_3d_renewalplus_aniso",
                 "world_3d_renewalplus", "multires_world", "nonstat_bruteforce_iso", "nonstat_bruteforce_world_var", "nonstat_bruteforce_1d_renewalplus",
                 "multires_1d_xy", "multires_1d_renewal", "grid_var_bruteforce_iso", "grid_ls_multires_iso", "grid_ls_var_multires_1d",
-                "proc_mean_two_spheres_iso", "proc_mean_grid_sdf_iso", "proc_mean_knob_inner_1d"]
+                "proc_mean_two_spheres_iso", "proc_mean_grid_sdf_iso", "proc_mean_knob_inner_1d", "aniso_mtx_iso_renewalplus", "aniso_mtx_multires_iso",
+                "fbm_sandstone_var_bruteforce_iso", "fbm_rust_ls_multires_iso"]
 
 
 def checker(medium_json):
