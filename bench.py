@@ -264,6 +264,7 @@ def run_gpu(args):
     if not args.no_extras:
         queries = {}
         nq = 1 << 20
+        qclock = ClockSampler(local); qclock.start()
         for key, name in (("C1", "c1_sphere_3d_none"), ("C3", "c3_1d_renewal"), ("C4", "c4_1d_renewalplus_xy_mis"), ("C5", "c5_multires_nonstat_renewalplus")):
             g = S.GpuImpl(S.MEDIA[name], device=local)
             row = {"medium": name, "kernel": g.m.info()["query_kernel"], "rays": nq}
@@ -320,6 +321,15 @@ def run_gpu(args):
                                "api": "scn_sample_distance_batch_host (C1 medium, 2^20 camera rays; pinned host SoA rays + state in, samples + state out; one stream per stage)"}
                 gh.close()
             g.close()
+        qclock.stop()
+        qck = torch.tensor([qclock.summary()["sm_mhz"] or 0.0], device=dev, dtype=torch.float64)
+        if world > 1:
+            allc = [torch.zeros_like(qck) for _ in range(world)]
+            dist.all_gather(allc, qck)
+            queries["per_rank_sm_mhz"] = [float(t_.item()) for t_ in allc]
+        else:
+            queries["per_rank_sm_mhz"] = [float(qck.item())]
+        queries["clock_reasons"] = qclock.summary()["reasons"]
 
     # ---- tile-sharded wavefront renders at the BASELINE.json sizes: every rank renders its tiles (round-robin ownership), one NCCL
     #      all_gather of the slices.  Strong scaling: the same image at every N.
@@ -334,19 +344,22 @@ def run_gpu(args):
             torch.cuda.synchronize()
             if world > 1:
                 dist.barrier()
-            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            a.record(stream); wr.render(spp); img = R.gather_image_rgb(wr, world); b.record(stream); torch.cuda.synchronize()
+            a, b, c_ = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            cs = ClockSampler(local); cs.start()
+            a.record(stream); wr.render(spp); c_.record(stream); img = R.gather_image_rgb(wr, world); b.record(stream); torch.cuda.synchronize()
+            cs.stop(); ck = cs.summary()
             tr = torch.tensor([a.elapsed_time(b)], device=dev, dtype=torch.float64)
-            per_rank = [float(tr.item())]
-            if world > 1:  # every rank's own time (the render is as slow as its slowest rank: load balance and per-GPU speed are both in here)
-                allt = [torch.zeros_like(tr) for _ in range(world)]
-                dist.all_gather(allt, tr)
-                per_rank = [float(t_.item()) for t_ in allt]
+            own = torch.tensor([a.elapsed_time(c_), ck["sm_mhz"] or 0.0], device=dev, dtype=torch.float64)  # this rank's tiles, before the gather
+            per_rank, per_rank_mhz = [float(own[0].item())], [float(own[1].item())]
+            if world > 1:  # the render is as slow as its slowest rank: load balance and per-GPU speed (clock) are both in here
+                allt = [torch.zeros_like(own) for _ in range(world)]
+                dist.all_gather(allt, own)
+                per_rank = [float(t_[0].item()) for t_ in allt]; per_rank_mhz = [float(t_[1].item()) for t_ in allt]
                 dist.all_reduce(tr, op=dist.ReduceOp.MAX)
             res = sc["camera"]["resolution"]
             out = {"workload": "%s %dx%d @%dspp, max_bounces %d, nee %s, 16x16 tiles over %d GPU(s) (%s), one all_gather" % (label, res[0], res[1], spp, sc["integrator"]["max_bounces"], "on" if wr.nee else "off", world, wr.sharding),
                    "ms": float(tr.item()), "camera_paths": res[0] * res[1] * spp, "camera_paths_per_s": res[0] * res[1] * spp / (float(tr.item()) * 1e-3), "mean_radiance": float(img.mean().item()),
-                   "per_rank_ms": [round(v, 3) for v in per_rank]}
+                   "per_rank_render_ms": [round(v, 3) for v in per_rank], "per_rank_sm_mhz": per_rank_mhz, "clock_reasons": ck["reasons"]}
             wr.close()
             return out
 

@@ -499,9 +499,13 @@ SCN_FN double proc_mean(const scn_mean_desc &md, const FieldK &f, dbl3 a) {
     const float r = xadd(m, md.offset);
     return (double)(md.min > r ? md.min : r);
 }
+// PROC = false: the cached march kernels (scn_march.cuh, scn_march1d.cuh) are compiled without the procedural mean — a reachable call
+// into the procedural-field code costs them their spill-free register allocation (406 B of spills in the stationary 3D kernel, -15 %) —
+// and media with such a mean are served by the generic kernels (march_block_size / march1d_supported).
+template <bool PROC = true>
 SCN_HD double mean_eval(const scn_mean_desc &md, const FieldK &mf, dbl3 a) {
     switch (md.type) {
-    case SCN_MEAN_PROCEDURAL: return proc_mean(md, mf, a);
+    case SCN_MEAN_PROCEDURAL: return PROC ? proc_mean(md, mf, a) : 0.;
     case SCN_MEAN_HOMOGENEOUS: return (double)md.offset;
     case SCN_MEAN_SPHERICAL: {
         double qx = ysub(a.x, md.center[0]), qy = ysub(a.y, md.center[1]), qz = ysub(a.z, md.center[2]);
@@ -515,14 +519,15 @@ SCN_HD double mean_eval(const scn_mean_desc &md, const FieldK &mf, dbl3 a) {
     default: return 0.;
     }
 }
+template <bool PROC = true>
 SCN_HD f3 mean_grad(const scn_mean_desc &md, const FieldK &mf, dbl3 a) {
     switch (md.type) {
-    case SCN_MEAN_PROCEDURAL: { // ProceduralMean::dmean_da (math/GPFunctions.cpp:287-296): forward differences, eps = double(0.001f)
+    case SCN_MEAN_PROCEDURAL: if (PROC) { // ProceduralMean::dmean_da (math/GPFunctions.cpp:287-296): forward differences, eps = double(0.001f)
         const double eps = (double)0.001f;
         dbl3 ax = a, ay = a, az = a; ax.x = yadd(a.x, eps); ay.y = yadd(a.y, eps); az.z = yadd(a.z, eps);
         const double v0 = proc_mean(md, mf, a), v1 = proc_mean(md, mf, ax), v2 = proc_mean(md, mf, ay), v3 = proc_mean(md, mf, az);
         return F3((float)ydiv(ysub(v1, v0), eps), (float)ydiv(ysub(v2, v0), eps), (float)ydiv(ysub(v3, v0), eps));
-    }
+    } else return F3(0.f, 0.f, 0.f);
     case SCN_MEAN_SPHERICAL: {
         double qx = ysub(a.x, md.center[0]), qy = ysub(a.y, md.center[1]), qz = ysub(a.z, md.center[2]);
         double inv = ydiv(1.0, ysqrt(yadd(yadd(ymul(qx, qx), ymul(qy, qy)), ymul(qz, qz))));
@@ -537,12 +542,15 @@ SCN_HD f3 mean_grad(const scn_mean_desc &md, const FieldK &mf, dbl3 a) {
     default: return F3(0.f, 0.f, 0.f);
     }
 }
+template <bool PROC = true>
 SCN_HD void gp_mean_and_id(const Params &P, f3 p, double &mean, int &id) {
     dbl3 a = to_dbl3(p);
-    mean = mean_eval(P.mean, P.mean_f, a); id = P.gp_id;
-    if (P.has_mean_add) { double v = mean_eval(P.mean_add, P.mean_add_f, a); if (v < mean) { mean = v; id = P.id_add; } }
+    mean = mean_eval<PROC>(P.mean, P.mean_f, a); id = P.gp_id;
+    if (P.has_mean_add) { double v = mean_eval<PROC>(P.mean_add, P.mean_add_f, a); if (v < mean) { mean = v; id = P.id_add; } }
 }
-SCN_HD f3 gp_mean_grad(const Params &P, f3 p, int id) { return id == P.gp_id ? mean_grad(P.mean, P.mean_f, to_dbl3(p)) : mean_grad(P.mean_add, P.mean_add_f, to_dbl3(p)); }
+template <bool PROC = true>
+SCN_HD f3 gp_mean_grad(const Params &P, f3 p, int id) { return id == P.gp_id ? mean_grad<PROC>(P.mean, P.mean_f, to_dbl3(p)) : mean_grad<PROC>(P.mean_add, P.mean_add_f, to_dbl3(p)); }
+SCN_HD bool has_procedural_mean(const Params &P) { return P.mean.type == SCN_MEAN_PROCEDURAL || (P.has_mean_add && P.mean_add.type == SCN_MEAN_PROCEDURAL); }
 
 // ---------------------------------------------------------------- seeds and multi-resolution levels
 SCN_HD uint32_t compute_seed(const Params &P, const Info &in) { // SCN:40-49

@@ -30,7 +30,7 @@
 namespace scn {
 
 inline bool march1d_supported(const Params &P) {
-    return P.sampling_1d && !P.use_mtx && !P.has_aniso && P.kernel == SCN_COV_SQUARED_EXPONENTIAL && P.n_imp >= 1 && P.n_imp <= 4;
+    return P.sampling_1d && !P.use_mtx && !P.has_aniso && P.kernel == SCN_COV_SQUARED_EXPONENTIAL && P.n_imp >= 1 && P.n_imp <= 4 && !has_procedural_mean(P);
 }
 
 #if defined(__CUDACC__)
@@ -296,7 +296,7 @@ __global__ void __launch_bounds__(MARCH1D_BLOCK, VAR == 0 ? 5 : (VAR == 1 ? 4 : 
         }
         if (active) {
             const float amp = VAR == 0 ? P.sigma : cov_amplitude(P, p); // stationary instantiations carry no procedural-field code
-            double mean; gp_mean_and_id(P, p, mean, id);
+            double mean; gp_mean_and_id<false>(P, p, mean, id);
             if (P.surf_vol_sep) id = 1.f < P.surf_vol_thresh ? 0 : 1;
             fval = (float)yadd((double)xmul(amp, nv), mean);
         }
