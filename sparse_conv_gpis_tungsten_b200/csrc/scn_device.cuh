@@ -230,7 +230,10 @@ SCN_FN double fbm_rust(dbl3 p, int oct, double sign) {
     const double x = clamp01_d(ydiv(ysub(v, 0.4), ysub(0.6, 0.4)));
     return ymul(ymul(x, x), ysub(3.0, ymul(2.0, x))); // smoothStep (math/MathUtil.hpp:108-112)
 }
-SCN_FN double field_scalar(const FieldK &k, dbl3 p) {
+// FULL = false (the iso-ray instantiations of k_march for media whose fields are constants / ramps): the grid and fbm fields are compiled
+// out, because a reachable call chain into them costs the two-level kernel its register allocation (C5: 92 B of spills, 32.6 -> 29.3 M queries/s).
+SCN_HD bool field_is_heavy(const FieldK &k) { return k.type == SCN_FIELD_REGULAR_GRID || k.type == SCN_FIELD_SANDSTONE || k.type == SCN_FIELD_RUST; }
+SCN_FN double field_scalar_heavy(const FieldK &k, dbl3 p) {
     switch (k.type) {
     case SCN_FIELD_SANDSTONE: { // ProceduralNoise::operator() (GPF:70-77)
         const double f = fbm_sandstone(p, 2);
@@ -238,7 +241,13 @@ SCN_FN double field_scalar(const FieldK &k, dbl3 p) {
         return yadd(ymul(k.fmin, ysub(1.0, t)), ymul(k.fmax, t));
     }
     case SCN_FIELD_RUST: { const double t = clamp01_d(fbm_rust(p, 2, -1.0)); return yadd(ymul(k.fmin, ysub(1.0, t)), ymul(k.fmax, t)); } // GPF:78-83
-    case SCN_FIELD_REGULAR_GRID: return field_grid(k, p, 0);
+    default: return field_grid(k, p, 0);
+    }
+}
+template <bool FULL = true>
+SCN_FN double field_scalar(const FieldK &k, dbl3 p) {
+    if (FULL && field_is_heavy(k)) return field_scalar_heavy(k, p);
+    switch (k.type) {
     case SCN_FIELD_CONSTANT: return k.val[0];
     case SCN_FIELD_BOTTOM_TOP: return field_ramp(k, p.y, 0) - 1.;
     case SCN_FIELD_LEFT_RIGHT: return field_ramp(k, p.x, 0) - 1.;
@@ -250,9 +259,7 @@ SCN_FN double field_scalar(const FieldK &k, dbl3 p) {
 SCN_HD dbl3 to_dbl3(f3 p) { dbl3 r; r.x = p.x; r.y = p.y; r.z = p.z; return r; }
 
 // ---------------------------------------------------------------- covariance helpers (see oracle/scn_oracle.c for the line map)
-SCN_HD float cov_lateral_scale(const Params &P, f3 p) { // sparseConvNoiseLateralScale
-    if (P.stationary || P.ls.type == SCN_FIELD_NONE) return 1.0f;
-    if (P.ls.type == SCN_FIELD_CONSTANT) return max3((float)P.ls.val[0], (float)P.ls.val[1], (float)P.ls.val[2]);
+SCN_FN float cov_lateral_scale_heavy(const Params &P, f3 p) {
     if (P.ls.type == SCN_FIELD_SANDSTONE) { // ProceduralNoiseVec::operator() (GPF:104-111): clamp(col * 0.2, 0, 1), 10 octaves; largest component
         const double f = fbm_sandstone(to_dbl3(p), 10);
         const double c0 = clamp01_d(ymul(ysub(sqrt(ymul(ymul(f, 1.9), 1.2)), 0.35), 0.2)), c1 = clamp01_d(ymul(ysub(sqrt(ymul(ymul(f, 0.7), 1.2)), 0.35), 0.2)),
@@ -263,19 +270,26 @@ SCN_HD float cov_lateral_scale(const Params &P, f3 p) { // sparseConvNoiseLatera
         const double f = fbm_rust(to_dbl3(p), 10, 1.0), g = ysub(1.0, f);
         return max3((float)yadd(ymul(0.278, g), ymul(1.0, f)), (float)yadd(ymul(0.212, g), ymul(1.0, f)), (float)yadd(ymul(0.141, g), ymul(1.0, f)));
     }
-    if (P.ls.type == SCN_FIELD_REGULAR_GRID) { // getKernelScale (GPF:1729-1735): Vec3f of the interpolated Vec3d, largest component
-        const dbl3 q = to_dbl3(p);
-        return max3((float)field_grid(P.ls, q, 0), (float)field_grid(P.ls, q, 1), (float)field_grid(P.ls, q, 2));
-    }
-    return (float)field_scalar(P.ls, to_dbl3(p));
+    // regular_grid: getKernelScale (GPF:1729-1735): Vec3f of the interpolated Vec3d, largest component
+    const dbl3 q = to_dbl3(p);
+    return max3((float)field_grid(P.ls, q, 0), (float)field_grid(P.ls, q, 1), (float)field_grid(P.ls, q, 2));
 }
+template <bool FULL = true>
+SCN_HD float cov_lateral_scale(const Params &P, f3 p) { // sparseConvNoiseLateralScale
+    if (P.stationary || P.ls.type == SCN_FIELD_NONE) return 1.0f;
+    if (P.ls.type == SCN_FIELD_CONSTANT) return max3((float)P.ls.val[0], (float)P.ls.val[1], (float)P.ls.val[2]);
+    if (FULL && field_is_heavy(P.ls)) return cov_lateral_scale_heavy(P, p);
+    return (float)field_scalar<false>(P.ls, to_dbl3(p));
+}
+template <bool FULL = true>
 SCN_HD float cov_ns_scale(const Params &P, f3 p) { // nonStationarySplattingKernelScale
     if (P.stationary || P.multires) return 1.f;
-    return xdiv(cov_lateral_scale(P, p), P.ls_max);
+    return xdiv(cov_lateral_scale<FULL>(P, p), P.ls_max);
 }
+template <bool FULL = true>
 SCN_HD float cov_amplitude(const Params &P, f3 p) { // sparseConvNoiseAmplitude
     if (P.stationary) return P.sigma;
-    double var = P.var.type != SCN_FIELD_NONE ? field_scalar(P.var, to_dbl3(p)) : 1.;
+    double var = P.var.type != SCN_FIELD_NONE ? field_scalar<FULL>(P.var, to_dbl3(p)) : 1.;
     return (float)(var * (double)P.sigma);
 }
 SCN_HD float tr_scale(const Params &P, float s) { return P.stationary ? s : (P.multires ? s : P.ls_max); }
@@ -562,8 +576,9 @@ struct Levels { float s_lo, s_hi, r_lo, r_hi; int k_lo; };
 // kernelScaleLevelRatio (SCN:60-70).  The level index is floor(logf(ls)/logf(2.5f)) on the CPU; the device takes
 // log in double and rounds to float (== the correctly rounded logf in all but double-rounding corner cases), and
 // reads 2.5^k from the host-computed table so that the grid scaling matches the reference's powf bit for bit.
+template <bool FULL = true>
 SCN_FN Levels level_ratio(const Params &P, f3 p) {
-    float ls = cov_lateral_scale(P, p);
+    float ls = cov_lateral_scale<FULL>(P, p);
     float lg = (float)log((double)ls);
     float lo = floorf(xdiv(lg, P.log_base)); // logf(2.5f) from the host libm
     int k = (int)lo;
