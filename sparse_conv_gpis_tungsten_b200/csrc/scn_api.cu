@@ -392,6 +392,20 @@ int scn_nee_grad_batch(const scn_medium *m, const scn_nee_in *in, float *gx, flo
     return nee_impl(m, in, nullptr, gx, gy, gz, n, stream);
 }
 
+// debug build only (-DSCN_DEBUG_BOUNDS, tools/debug_bounds.py; not declared in include/scn.h): the eight assertion counters of the tuned
+// kernels (scn_device.cuh: SCN_CHECK), read and cleared.  The product build answers SCN_EUNSUPPORTED.
+int scn_debug_bounds_failures(unsigned long long out[8]) {
+#if defined(SCN_DEBUG_BOUNDS)
+    cudaError_t e = cudaMemcpyFromSymbol(out, g_scn_bounds_fail, 8 * sizeof(unsigned long long));
+    if (e != cudaSuccess) return cuda_fail(e, "scn_debug_bounds_failures");
+    unsigned long long z[8] = {0};
+    e = cudaMemcpyToSymbol(g_scn_bounds_fail, z, sizeof z);
+    return e == cudaSuccess ? SCN_OK : cuda_fail(e, "scn_debug_bounds_failures");
+#else
+    (void)out; return set_error(SCN_EUNSUPPORTED, "built without SCN_DEBUG_BOUNDS");
+#endif
+}
+
 // test hook: serve this medium with the one-thread-per-ray generic kernels even where a tuned kernel covers it
 int scn_debug_force_generic(scn_medium *m, int on) {
     if (!m) return set_error(SCN_EINVAL, "null argument");

@@ -36,6 +36,20 @@ struct Frame { f3 n, t, b; };
 struct Coeff { float vs; f3 gs; f3 org; };                 // SparseConvConditioningCoefficients3D/1D
 struct Info { uint32_t px, py, spp, seg, scene_seed; float t; }; // RayInfo
 
+// ---------------------------------------------------------------- bounds checks of the tuned kernels (debug build only)
+// compute-sanitizer is closed on this pool (profiles/r02_compute_sanitizer_closed_on_pool.txt), so the checks it would make on the cached
+// march kernels are written out: -DSCN_DEBUG_BOUNDS (tools/debug_bounds.py builds that library next to the product one) counts every
+// violated index / capacity assertion in a device counter and poisons the shared-memory caches with NaN at kernel start, so that a read of a
+// slot that was never written shows up as a changed result.  The product build compiles all of it out.
+#if defined(SCN_DEBUG_BOUNDS) && defined(__CUDACC__)
+static __device__ unsigned long long g_scn_bounds_fail[8];
+#define SCN_CHECK(cond, code) do { if (!(cond)) atomicAdd(&g_scn_bounds_fail[code], 1ULL); } while (0)
+#define SCN_SMEM_FILL __int_as_float(0x7fc00000)
+#else
+#define SCN_CHECK(cond, code) ((void)0)
+#define SCN_SMEM_FILL 0.f
+#endif
+
 // ---------------------------------------------------------------- exactly rounded primitives
 #if defined(__CUDA_ARCH__)
 SCN_HD float xmul(float a, float b) { return __fmul_rn(a, b); }

@@ -204,7 +204,7 @@ __global__ void __launch_bounds__(MARCH1D_BLOCK, VAR == 0 ? 5 : (VAR == 1 ? 4 : 
                 const unsigned idx = base + __popc(mf & lt);
                 if (idx >= A.n) phase = PH_EXIT;
                 else {
-                    ri = idx;
+                    ri = idx; SCN_CHECK(ri < A.n, 6);
                     const f3 pos = F3(A.r.ox[ri], A.r.oy[ri], A.r.oz[ri]), dir = F3(A.r.dx[ri], A.r.dy[ri], A.r.dz[ri]);
                     near_t = A.r.tmin[ri]; float far_t = A.r.tmax[ri]; const float u = A.r.u[ri];
                     if (!isfinite(far_t)) far_t = (float)((double)near_t + 2000.0); // GPM:229-231
@@ -335,6 +335,7 @@ __global__ void __launch_bounds__(MARCH1D_BLOCK, VAR == 0 ? 5 : (VAR == 1 ? 4 : 
             finished = true; hit = false; t_fin = dfar; last_val = fval;
         }
         if (finished) {
+            SCN_CHECK(ri < A.n && active, 7);
             if (TRANSMIT) { // GPM:343-393: the gradient at a crossing is evaluated (one more evaluation) but cannot change T
                 A.T[ri] = hit ? 0.f : 1.f;
                 if (A.n_evals) A.n_evals[ri] = evals + (hit ? 1u : 0u);

@@ -5,6 +5,7 @@
 #   queries    queries/s of the BASELINE media (tools/run_queries.py)
 #   launches   ncu launch list of the bench command (gpu__time_duration.sum)
 #   ncu_fast | ncu_c1 | ncu_c5 | ncu_c3     one `ncu --set full` capture of that kernel
+#   ncu_report condense the captures of this TAG into *_summary.txt on the box and delete them (they are too large to travel back)
 #   sanitize   compute-sanitizer memcheck / racecheck / initcheck over tools/sanitize_workload.py
 # Everything is written under gpurun_out/ (scratch); what is to be judged is copied into profiles/ afterwards.
 set -x; mkdir -p gpurun_out; T=${TAG:-r02}
@@ -31,6 +32,13 @@ ncu_c5)
   $NCU -k regex:k_march --launch-skip 1 -c 1 -f -o gpurun_out/march_c5_$T python tools/run_queries.py c5_multires_nonstat_renewalplus 20 1 > gpurun_out/ncu_march_c5_$T.log 2>&1 ;;
 ncu_c3)
   $NCU -k regex:k_march1d --launch-skip 1 -c 1 -f -o gpurun_out/march1d_$T python tools/run_queries.py c3_1d_renewal 20 1 > gpurun_out/ncu_march1d_$T.log 2>&1 ;;
+ncu_report)
+  # condense every capture ON THE BOX (four .ncu-rep files exceed the 64 MiB that travel back) and drop the captures
+  for rep in gpurun_out/*_$T.ncu-rep; do
+    out=${rep%.ncu-rep}_summary.txt
+    { python tools/ncu_summary.py $rep; python tools/ncu_brief.py $rep; python tools/ncu_footprint.py $rep; python tools/ncu_blocks.py $rep 1.0; python tools/ncu_lines.py $rep 0.8 3e6; } > $out 2>&1
+    rm -f $rep
+  done ;;
 sanitize)
   for tool in memcheck racecheck initcheck; do
     timeout 900 compute-sanitizer --tool $tool --print-limit 20 python tools/sanitize_workload.py 13 > gpurun_out/sanitize_${tool}_$T.log 2>&1
