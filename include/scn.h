@@ -110,6 +110,8 @@ typedef struct scn_field_desc {
 #define SCN_SDF_KNOB_INNER 1   /* "knob_inner": sphere of radius 0.75 in the 0.8-scaled frame (math/SdfFunctions.cpp:148-157) */
 #define SCN_SDF_TWO_SPHERES 2  /* "two_spheres" (math/SdfFunctions.cpp:181-183)                                               */
 #define SCN_SDF_PLANE 3        /* "plane": p.y (math/SdfFunctions.hpp:53)                                                     */
+#define SCN_SDF_KNOB 4         /* "knob": the material-test knob (math/SdfFunctions.cpp:100-145): sphere, cut-outs, torus etch, cone base */
+#define SCN_SDF_KNOB_OUTER 5   /* "knob_outer" (math/SdfFunctions.cpp:159-179)                                                */
 
 /* mean function: math/GPFunctions.hpp:867-1005 (homogeneous, spherical, linear), :1049-1087 + math/GPFunctions.cpp:250-296 (procedural) */
 typedef struct scn_mean_desc {

@@ -551,6 +551,60 @@ static void cov_kernel1d(const orc_medium *m, float pq, float pc, v3 pc_world, f
 static float cov_c1d_ls(const orc_medium *m, v3 pqw, v3 pcw) { return m->stationary ? 1.0f : cov_splat_cov1d(m, pqw, pcw); }
 
 /* ------------------------------------------------------------------ mean (GPF.hpp:867-1005, GaussianProcess.cpp:379-393) */
+/* the material-test knob (math/SdfFunctions.cpp:66-179); expressions keep the reference's literal types (double literals promote) */
+static const float SDF_PI = 3.1415926536f;
+static float sdf_minf(float a, float b) { return a < b ? a : b; }
+static float sdf_maxf(float a, float b) { return a > b ? a : b; }
+static float sdf_len2(float x, float y) { float s = x * x; s += y * y; return sqrtf(s); }
+static float sdf_len3(float x, float y, float z) { float s = x * x; s += y * y; s += z * z; return sqrtf(s); }
+static void sdf_rotx(float deg, const float *b, float *o) { /* Mat4f::rotAxis((1,0,0), deg).transformVector (math/Mat4f.cpp:132-148, Mat4f.hpp:159-166) */
+    float angle = deg * (SDF_PI / 180.0f), s = sinf(angle), c = cosf(angle), c1 = 1.0f - c, x = 1.f, y = 0.f, z = 0.f;
+    float m[9] = {c + x * x * c1, x * y * c1 - z * s, x * z * c1 + y * s, y * x * c1 + z * s, c + y * y * c1, y * z * c1 - x * s, z * x * c1 - y * s, z * y * c1 + x * s, c + z * z * c1};
+    for (int i = 0; i < 3; ++i) o[i] = m[3 * i] * b[0] + m[3 * i + 1] * b[1] + m[3 * i + 2] * b[2];
+}
+static float sdf_cone(const float *p, float cx, float cy) { float q = sdf_len2(p[0], p[1]); float s = cx * q; s += cy * p[2]; return s; }
+static float sdf_capped_cylinder(const float *p, float h, float r) {
+    float dx = fabsf(sdf_len2(p[0], p[2])) - h, dy = fabsf(p[1]) - r;
+    return sdf_minf(sdf_maxf(dx, dy), 0.0f) + sdf_len2(sdf_maxf(dx, 0.0f), sdf_maxf(dy, 0.0f));
+}
+static float sdf_tri_prism(const float *p, float hx, float hy) {
+    float qx = fabsf(p[0]), qz = fabsf(p[2]);
+    return sdf_maxf(qz - hy, sdf_maxf(qx * 0.866025f + p[1] * 0.5f, -p[1]) - hx * 0.5f);
+}
+static float sdf_lerpf(float a, float b, float r) { return a * (1.0f - r) + b * r; }
+static float sdf_smooth_union(float d1, float d2, float k) {
+    float h = 0.5f + 0.5f * (d2 - d1) / k; h = sdf_minf(sdf_maxf(h, 0.0f), 1.0f);
+    return sdf_lerpf(d2, d1, h) - k * h * (1.0 - h);
+}
+static float sdf_ssub(float d1, float d2, float k) {
+    float h = clampd(0.5 - 0.5 * (d2 + d1) / k, 0.0, 1.0);
+    return sdf_lerpf(d2, -d1, h) + k * h * (1.0 - h);
+}
+static float sdf_base(const float *p) {
+    float a[3] = {p[0], p[1] + .9f, p[2]}, b[3] = {p[0], p[1] - .9f, p[2]}, ra[3], rb[3], c[3] = {p[0], p[1], p[2] + -1.f}, rc[3];
+    sdf_rotx(-90, a, ra); sdf_rotx(90, b, rb);
+    float base = sdf_smooth_union(sdf_cone(ra, (float)(SDF_PI / 3.), (float)(SDF_PI / 3.)), sdf_cone(rb, SDF_PI / 3.f, SDF_PI / 3.f), 0.02);
+    base = sdf_maxf(base, sdf_capped_cylinder(p, 1.1f, 0.25f)) * 0.7f;
+    base = sdf_maxf(-sdf_capped_cylinder(p, 0.6f, 0.3f), base);
+    sdf_rotx(90, c, rc);
+    base = sdf_maxf(-sdf_tri_prism(rc, 1.2f, 0.3f), base);
+    return base;
+}
+static float sdf_knob(float x, float y, float z, int outer) {
+    const float scale = 0.8f; float k = (float)(1. / scale);
+    float p[3] = {x * k, y * k, z * k};
+    float sphere = sdf_len3(p[0], p[1], p[2]) - 1.0f, cutout = sdf_len3(p[0], p[1] - 0.5f, p[2] - 0.5f) - 0.7f;
+    float e[3] = {p[0], p[1] - 0.2f, p[2] - 0.2f}, te[3];
+    sdf_rotx(-45, e, te);
+    float etch = sdf_len2(sdf_len2(te[0], te[2]) - 1.0f, te[1]) - 0.05f;
+    float inner = sdf_len3(p[0], p[1], p[2]) - 0.75f;
+    float d = sdf_ssub(cutout, sphere, 0.1);
+    d = outer ? sdf_maxf(d, -inner) : sdf_minf(d, inner);
+    d = sdf_maxf(-etch, d);
+    float q[3] = {p[0], p[1] - -.775f, p[2]};
+    d = sdf_minf(sdf_ssub(sphere, sdf_base(q), 0.1), d);
+    return d * scale;
+}
 /* ProceduralMean::mean (GPF:279-285) over SdfFunctions::eval (math/SdfFunctions.hpp:47-55, SdfFunctions.cpp:148-157, 181-183) or the scalar field "f" */
 static double proc_mean(const scn_mean_desc *md, d3 a) {
     float px = (float)a.x, py = (float)a.y, pz = (float)a.z;
@@ -569,6 +623,8 @@ static double proc_mean(const scn_mean_desc *md, d3 a) {
         float qx = x * k, qy = y * k, qz = z * k;
         m = (sqrtf(qx * qx + qy * qy + qz * qz) - 0.75f) * scale; break;
     }
+    case SCN_SDF_KNOB: m = sdf_knob(x, y, z, 0); break;
+    case SCN_SDF_KNOB_OUTER: m = sdf_knob(x, y, z, 1); break;
     default: { d3 q = {x, y, z}; m = (float)field_scalar(&md->f, q); break; }
     }
     m *= md->scale;

@@ -40,7 +40,7 @@ class MeanDesc(C.Structure):
 
 
 MEAN_PROCEDURAL = 3
-SDF_FIELD, SDF_KNOB_INNER, SDF_TWO_SPHERES, SDF_PLANE = 0, 1, 2, 3
+SDF_FIELD, SDF_KNOB_INNER, SDF_TWO_SPHERES, SDF_PLANE, SDF_KNOB, SDF_KNOB_OUTER = 0, 1, 2, 3, 4, 5
 
 
 class MediumDesc(C.Structure):

@@ -505,7 +505,55 @@ SCN_HD float se_c1d_grad2_normal(float ab, float ls) { float den = 4.0f * ls * l
 // ---------------------------------------------------------------- mean (GPF.hpp:867-1005, GaussianProcess.cpp:379-393) in double
 // ProceduralMean::mean (math/GPFunctions.cpp:279-285): the point goes to float, through the inverse config transform
 // (Mat4f::transformPoint, math/Mat4f.hpp:168-175), into the SDF function (math/SdfFunctions.cpp) or the scalar field; float scale / offset / floor.
-SCN_FN double proc_mean(const scn_mean_desc &md, const FieldK &f, dbl3 a) {
+// ---- the material-test knob (math/SdfFunctions.cpp:66-179), float arithmetic in the reference's order; double where its literals promote
+SCN_HD float sdf_min(float a, float b) { return a < b ? a : b; } // math/MathUtil.hpp:14-29
+SCN_HD float sdf_max(float a, float b) { return a > b ? a : b; }
+SCN_HD float sdf_len2(float x, float y) { return xsqrt(xadd(xmul(x, x), xmul(y, y))); }
+SCN_HD float sdf_len3(f3 v) { return xsqrt(xlensq(v)); }
+SCN_HD f3 sdf_rotx(const float *r, f3 b) { // Mat4f::rotAxis((1,0,0), .).transformVector (math/Mat4f.hpp:159-166): rows (a11,0,0), (0,c,-s), (0,s,c)
+    return F3(xadd(xadd(xmul(r[0], b.x), xmul(0.f, b.y)), xmul(0.f, b.z)), xadd(xadd(xmul(0.f, b.x), xmul(r[1], b.y)), xmul(-r[2], b.z)),
+              xadd(xadd(xmul(0.f, b.x), xmul(r[2], b.y)), xmul(r[1], b.z)));
+}
+SCN_HD float sdf_cone(f3 p, float c) { return xadd(xmul(c, sdf_len2(p.x, p.y)), xmul(c, p.z)); }
+SCN_HD float sdf_capped_cylinder(f3 p, float h, float r) {
+    const float dx = xsub(fabsf(sdf_len2(p.x, p.z)), h), dy = xsub(fabsf(p.y), r);
+    return xadd(sdf_min(sdf_max(dx, dy), 0.0f), sdf_len2(sdf_max(dx, 0.0f), sdf_max(dy, 0.0f)));
+}
+SCN_HD float sdf_tri_prism(f3 p, float hx, float hy) {
+    const f3 q = F3(fabsf(p.x), fabsf(p.y), fabsf(p.z));
+    return sdf_max(xsub(q.z, hy), xsub(sdf_max(xadd(xmul(q.x, 0.866025f), xmul(p.y, 0.5f)), -p.y), xmul(hx, 0.5f)));
+}
+SCN_HD float sdf_smooth_union(float d1, float d2, float k) { // opSmoothUnion: lerp(d2, d1, h) - k h (1.0 - h), the last factor in double
+    float h = xadd(0.5f, xdiv(xmul(0.5f, xsub(d2, d1)), k)); h = sdf_min(sdf_max(h, 0.0f), 1.0f);
+    const float l = xadd(xmul(d2, xsub(1.0f, h)), xmul(d1, h));
+    return (float)ysub((double)l, ymul((double)xmul(k, h), ysub(1.0, (double)h)));
+}
+SCN_HD float sdf_ssub(float d1, float d2, float k) { // ssub: h in double, lerp(d2, -d1, h) + k h (1.0 - h)
+    double hd = ysub(0.5, ydiv(ymul(0.5, (double)xadd(d2, d1)), (double)k)); hd = hd > 0.0 ? hd : 0.0; hd = hd < 1.0 ? hd : 1.0;
+    const float h = (float)hd;
+    const float l = xadd(xmul(d2, xsub(1.0f, h)), xmul(-d1, h));
+    return (float)yadd((double)l, ymul((double)xmul(k, h), ysub(1.0, (double)h)));
+}
+SCN_FN float sdf_base(const float *kn, f3 p) { // sdBase
+    float base = sdf_smooth_union(sdf_cone(sdf_rotx(kn + 0, F3(p.x, xadd(p.y, .9f), p.z)), kn[9]), sdf_cone(sdf_rotx(kn + 3, F3(p.x, xsub(p.y, .9f), p.z)), kn[10]), 0.02f);
+    base = xmul(sdf_max(base, sdf_capped_cylinder(p, 1.1f, 0.25f)), 0.7f);
+    base = sdf_max(-sdf_capped_cylinder(p, 0.6f, 0.3f), base);
+    base = sdf_max(-sdf_tri_prism(sdf_rotx(kn + 3, F3(p.x, p.y, xadd(p.z, -1.f))), 1.2f, 0.3f), base);
+    return base;
+}
+SCN_FN float sdf_knob(const float *kn, f3 p0, bool outer) { // SdfFunctions::knob / knob_outer over sdKnob / sdKnobOuter
+    const f3 p = xscale3(p0, 1.25f); // p *= 1. / 0.8f
+    const float sphere = xsub(sdf_len3(p), 1.0f), cutout = xsub(sdf_len3(F3(p.x, xsub(p.y, 0.5f), xsub(p.z, 0.5f))), 0.7f);
+    const f3 te = sdf_rotx(kn + 6, F3(p.x, xsub(p.y, 0.2f), xsub(p.z, 0.2f)));
+    const float etch = xsub(sdf_len2(xsub(sdf_len2(te.x, te.z), 1.0f), te.y), 0.05f); // sdTorus(., (1, 0.05))
+    const float inner = xsub(sdf_len3(p), 0.75f);
+    float d = sdf_ssub(cutout, sphere, 0.1f);
+    d = outer ? sdf_max(d, -inner) : sdf_min(d, inner);
+    d = sdf_max(-etch, d);
+    d = sdf_min(sdf_ssub(sphere, sdf_base(kn, F3(p.x, xsub(p.y, -.775f), p.z)), 0.1f), d);
+    return xmul(d, 0.8f);
+}
+SCN_FN double proc_mean(const Params &P, const scn_mean_desc &md, const FieldK &f, dbl3 a) {
     const float px = (float)a.x, py = (float)a.y, pz = (float)a.z;
     const float *T = md.inv_transform;
     const f3 p = F3(xadd(xadd(xadd(xmul(T[0], px), xmul(T[1], py)), xmul(T[2], pz)), T[3]), xadd(xadd(xadd(xmul(T[4], px), xmul(T[5], py)), xmul(T[6], pz)), T[7]),
@@ -521,6 +569,8 @@ SCN_FN double proc_mean(const scn_mean_desc &md, const FieldK &f, dbl3 a) {
         const f3 q = xscale3(p, 1.25f);
         m = xmul(xsub(xsqrt(xlensq(q)), 0.75f), 0.8f); break;
     }
+    case SCN_SDF_KNOB: m = sdf_knob(P.knob_rot, p, false); break;
+    case SCN_SDF_KNOB_OUTER: m = sdf_knob(P.knob_rot, p, true); break;
     default: m = (float)field_scalar(f, to_dbl3(p)); break;
     }
     m = xmul(m, md.scale);
@@ -531,9 +581,9 @@ SCN_FN double proc_mean(const scn_mean_desc &md, const FieldK &f, dbl3 a) {
 // into the procedural-field code costs them their spill-free register allocation (406 B of spills in the stationary 3D kernel, -15 %) —
 // and media with such a mean are served by the generic kernels (march_block_size / march1d_supported).
 template <bool PROC = true>
-SCN_HD double mean_eval(const scn_mean_desc &md, const FieldK &mf, dbl3 a) {
+SCN_HD double mean_eval(const Params &P, const scn_mean_desc &md, const FieldK &mf, dbl3 a) {
     switch (md.type) {
-    case SCN_MEAN_PROCEDURAL: return PROC ? proc_mean(md, mf, a) : 0.;
+    case SCN_MEAN_PROCEDURAL: return PROC ? proc_mean(P, md, mf, a) : 0.;
     case SCN_MEAN_HOMOGENEOUS: return (double)md.offset;
     case SCN_MEAN_SPHERICAL: {
         double qx = ysub(a.x, md.center[0]), qy = ysub(a.y, md.center[1]), qz = ysub(a.z, md.center[2]);
@@ -548,12 +598,12 @@ SCN_HD double mean_eval(const scn_mean_desc &md, const FieldK &mf, dbl3 a) {
     }
 }
 template <bool PROC = true>
-SCN_HD f3 mean_grad(const scn_mean_desc &md, const FieldK &mf, dbl3 a) {
+SCN_HD f3 mean_grad(const Params &P, const scn_mean_desc &md, const FieldK &mf, dbl3 a) {
     switch (md.type) {
     case SCN_MEAN_PROCEDURAL: if (PROC) { // ProceduralMean::dmean_da (math/GPFunctions.cpp:287-296): forward differences, eps = double(0.001f)
         const double eps = (double)0.001f;
         dbl3 ax = a, ay = a, az = a; ax.x = yadd(a.x, eps); ay.y = yadd(a.y, eps); az.z = yadd(a.z, eps);
-        const double v0 = proc_mean(md, mf, a), v1 = proc_mean(md, mf, ax), v2 = proc_mean(md, mf, ay), v3 = proc_mean(md, mf, az);
+        const double v0 = proc_mean(P, md, mf, a), v1 = proc_mean(P, md, mf, ax), v2 = proc_mean(P, md, mf, ay), v3 = proc_mean(P, md, mf, az);
         return F3((float)ydiv(ysub(v1, v0), eps), (float)ydiv(ysub(v2, v0), eps), (float)ydiv(ysub(v3, v0), eps));
     } else return F3(0.f, 0.f, 0.f);
     case SCN_MEAN_SPHERICAL: {
@@ -573,11 +623,11 @@ SCN_HD f3 mean_grad(const scn_mean_desc &md, const FieldK &mf, dbl3 a) {
 template <bool PROC = true>
 SCN_HD void gp_mean_and_id(const Params &P, f3 p, double &mean, int &id) {
     dbl3 a = to_dbl3(p);
-    mean = mean_eval<PROC>(P.mean, P.mean_f, a); id = P.gp_id;
-    if (P.has_mean_add) { double v = mean_eval<PROC>(P.mean_add, P.mean_add_f, a); if (v < mean) { mean = v; id = P.id_add; } }
+    mean = mean_eval<PROC>(P, P.mean, P.mean_f, a); id = P.gp_id;
+    if (P.has_mean_add) { double v = mean_eval<PROC>(P, P.mean_add, P.mean_add_f, a); if (v < mean) { mean = v; id = P.id_add; } }
 }
 template <bool PROC = true>
-SCN_HD f3 gp_mean_grad(const Params &P, f3 p, int id) { return id == P.gp_id ? mean_grad<PROC>(P.mean, P.mean_f, to_dbl3(p)) : mean_grad<PROC>(P.mean_add, P.mean_add_f, to_dbl3(p)); }
+SCN_HD f3 gp_mean_grad(const Params &P, f3 p, int id) { return id == P.gp_id ? mean_grad<PROC>(P, P.mean, P.mean_f, to_dbl3(p)) : mean_grad<PROC>(P, P.mean_add, P.mean_add_f, to_dbl3(p)); }
 SCN_HD bool has_procedural_mean(const Params &P) { return P.mean.type == SCN_MEAN_PROCEDURAL || (P.has_mean_add && P.mean_add.type == SCN_MEAN_PROCEDURAL); }
 
 // ---------------------------------------------------------------- seeds and multi-resolution levels

@@ -64,6 +64,9 @@ struct Params {
     // GP
     int32_t gp_id, has_mean_add, id_add, _pad;
     scn_mean_desc mean, mean_add;
+    // the knob SDFs (math/SdfFunctions.cpp:100-179): Mat4f::rotAxis((1,0,0), -90 / +90 / -45 degrees) as {a11, cos, sin} each and the two
+    // "cone" constants Vec2f(PI / 3.) and Vec2f(PI / 3.f), all out of the host's libm / float arithmetic
+    float knob_rot[12]; // [0..8] the three rotations, [9] = float(PI / 3.), [10] = PI / 3.f
     FieldK mean_f, mean_add_f;  // procedural means: the scalar field "f" behind mean / mean_add (a regular_grid here points at device memory)
     FieldK ls, var;
     FieldK aniso_f;            // proc_nonstationary "aniso": rotation-anisotropy field (math/GPFunctions.cpp:1678-1690); has_aniso = field present

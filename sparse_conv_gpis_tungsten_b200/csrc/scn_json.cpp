@@ -245,6 +245,12 @@ void mat4Invert(const float a[16], float out[16]) {
     for (int i = 0; i < 16; ++i) out[i] = inv[i] * invDet;
 }
 
+int sdfFunction(const std::string &fn, int32_t &out) { // SdfFunctions::stringToFunction (math/SdfFunctions.cpp:22-36)
+    if (fn == "knob") out = SCN_SDF_KNOB; else if (fn == "knob_inner") out = SCN_SDF_KNOB_INNER; else if (fn == "knob_outer") out = SCN_SDF_KNOB_OUTER;
+    else if (fn == "two_spheres") out = SCN_SDF_TWO_SPHERES; else if (fn == "plane") out = SCN_SDF_PLANE;
+    else return set_error(SCN_EJSON, "Invalid function: '%s'", fn.c_str());
+    return SCN_OK;
+}
 int parseMean(const JVal &j, scn_mean_desc &m) {
     std::string type;
     if (!getS(j, "type", type)) return set_error(SCN_EJSON, "mean: missing \"type\"");
@@ -265,18 +271,15 @@ int parseMean(const JVal &j, scn_mean_desc &m) {
         for (int i = 0; i < 12; ++i) m.inv_transform[i] = inv[i];
         std::string fn = "knob";
         if (getS(j, "func", fn)) {
-            if (fn == "knob_inner") m.sdf_func = SCN_SDF_KNOB_INNER; else if (fn == "two_spheres") m.sdf_func = SCN_SDF_TWO_SPHERES; else if (fn == "plane") m.sdf_func = SCN_SDF_PLANE;
-            else if (fn == "knob" || fn == "knob_outer") return set_error(SCN_EUNSUPPORTED, "procedural mean: the material-test knob ('%s') is not covered (knob_inner, two_spheres, plane and field means are)", fn.c_str());
-            else return set_error(SCN_EJSON, "Invalid function: '%s'", fn.c_str());
+            if (int rc = sdfFunction(fn, m.sdf_func)) return rc;
         } else if (const JVal *f = j.get("f")) {
             m.sdf_func = SCN_SDF_FIELD;
             std::string ft; getS(*f, "type", ft);
             if (ft == "sdf") { // ProceduralSdf (math/GPFunctions.hpp:579-603): the same function table
                 std::string fs; getS(*f, "function", fs);
-                if (fs == "knob_inner") m.sdf_func = SCN_SDF_KNOB_INNER; else if (fs == "two_spheres") m.sdf_func = SCN_SDF_TWO_SPHERES; else if (fs == "plane") m.sdf_func = SCN_SDF_PLANE;
-                else return set_error(SCN_EUNSUPPORTED, "procedural mean: sdf function '%s' is not covered", fs.c_str());
+                if (int rc = sdfFunction(fs, m.sdf_func)) return rc;
             } else if (int rc = parseField(*f, m.f, false)) return rc;
-        } else return set_error(SCN_EUNSUPPORTED, "procedural mean without \"func\" or \"f\": the reference's default is the material-test knob, which is not covered");
+        } else m.sdf_func = SCN_SDF_KNOB; // ProceduralMean's default member: ProceduralSdf(Function::Knob) (math/GPFunctions.hpp:1052-1055, 581)
         getF(j, "min", m.min); getF(j, "scale", m.scale); getF(j, "offset", m.offset);
     } else if (type == "tabulated" || type == "mesh" || type == "neural")
         return set_error(SCN_EUNSUPPORTED, "mean type '%s' needs an OpenVDB grid / a mesh BVH / an MLP and is not covered", type.c_str());

@@ -81,7 +81,7 @@ int params_from_desc(const scn_medium_desc &d, Params &p) {
     if (d.mean.type < SCN_MEAN_HOMOGENEOUS || d.mean.type > SCN_MEAN_PROCEDURAL) return set_error(SCN_EINVAL, "bad mean type");
     for (const scn_mean_desc *md : {&d.mean, &d.mean_additional}) {
         if (md->type != SCN_MEAN_PROCEDURAL) continue;
-        if (md->sdf_func < SCN_SDF_FIELD || md->sdf_func > SCN_SDF_PLANE) return set_error(SCN_EINVAL, "procedural mean: bad sdf_func");
+        if (md->sdf_func < SCN_SDF_FIELD || md->sdf_func > SCN_SDF_KNOB_OUTER) return set_error(SCN_EINVAL, "procedural mean: bad sdf_func");
         if (md->sdf_func == SCN_SDF_FIELD && md->f.type == SCN_FIELD_NONE) return set_error(SCN_EINVAL, "procedural mean: neither a function nor a field");
     }
     if (!(d.impulse_density >= 0.f) || d.impulse_density > 4096.f) return set_error(SCN_EINVAL, "impulse_density out of range");
@@ -193,6 +193,14 @@ int params_from_desc(const scn_medium_desc &d, Params &p) {
         p.nf_world = std::sqrt((float)(per_unit * integral));
     }
     p.gp_id = d.gp_id; p.has_mean_add = d.has_mean_additional; p.id_add = d.id_additional;
+    {   // Mat4f::rotAxis (math/Mat4f.cpp:132-148) about (1, 0, 0): a11 = c + 1 * 1 * c1, the rotation block is (c, -s; s, c); Angle::degToRad = a * (PI / 180.0f)
+        const float PI_F = 3.1415926536f, angles[3] = {-90.f, 90.f, -45.f};
+        for (int i = 0; i < 3; ++i) {
+            const float a = angles[i] * (PI_F / 180.0f), sn = std::sin(a), cs = std::cos(a), c1 = 1.0f - cs;
+            p.knob_rot[3 * i] = cs + 1.0f * 1.0f * c1; p.knob_rot[3 * i + 1] = cs; p.knob_rot[3 * i + 2] = sn;
+        }
+        p.knob_rot[9] = (float)(PI_F / 3.); p.knob_rot[10] = PI_F / 3.f;
+    }
     p.mean = d.mean; p.mean_add = d.mean_additional;
     if (int rc = check_grid(d.mean.f, "mean.f")) return rc;
     if (int rc = check_grid(d.mean_additional.f, "mean_additional.f")) return rc;

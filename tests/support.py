@@ -149,6 +149,8 @@ MEDIA = {
                                         mean={"type": "procedural", "func": "two_spheres", "scale": 0.1, "transform": {"scale": [0.1, 0.1, 0.1], "position": [0, 0.05, 0]}}),
     "proc_mean_knob_inner_1d": medium(correlation_context="renewal", single_realization=False, mean={"type": "procedural", "f": {"type": "sdf", "function": "knob_inner"}, "min": -0.3},
                                       **{"1D_sampling": True}),
+    "proc_mean_knob_iso": medium(correlation_context="renewal+", single_realization=False, mean={"type": "procedural", "func": "knob", "transform": {"position": [0, 0.1, 0]}}),
+    "proc_mean_knob_outer_world": medium(isotropic_3D_sampling=False, mean={"type": "procedural", "func": "knob_outer", "scale": 1.1, "transform": {"rotation": [10, 40, 0]}}),
     "proc_mean_grid_sdf_iso": medium(correlation_context="renewal+", single_realization=False,
                                      mean={"type": "procedural", "f": _grid("torus12_sdf_linear"), "transform": {"rotation": [0, 0, 25]}}),
     # fbm fields "sandstone" / "rust" (math/GPFunctions.cpp:70-83, 104-117 over math/SdfFunctions.cpp:200-296: simplex noise on a sin() hash)
