@@ -345,21 +345,21 @@ def run_gpu(args):
             if world > 1:
                 dist.barrier()
             a, b, c_ = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            cs = ClockSampler(local); cs.start()
+            # (no nvidia-smi polling inside this region: a 20 ms poll loop contends with the render's ~500 launches per second for the driver
+            #  and cost the C4 render 12 % when it was tried; the clocks of the run are sampled in the headline and the query legs)
             a.record(stream); wr.render(spp); c_.record(stream); img = R.gather_image_rgb(wr, world); b.record(stream); torch.cuda.synchronize()
-            cs.stop(); ck = cs.summary()
             tr = torch.tensor([a.elapsed_time(b)], device=dev, dtype=torch.float64)
-            own = torch.tensor([a.elapsed_time(c_), ck["sm_mhz"] or 0.0], device=dev, dtype=torch.float64)  # this rank's tiles, before the gather
-            per_rank, per_rank_mhz = [float(own[0].item())], [float(own[1].item())]
-            if world > 1:  # the render is as slow as its slowest rank: load balance and per-GPU speed (clock) are both in here
+            own = torch.tensor([a.elapsed_time(c_)], device=dev, dtype=torch.float64)  # this rank's tiles, before the gather
+            per_rank = [float(own[0].item())]
+            if world > 1:  # the render is as slow as its slowest rank: load balance and per-GPU speed are both in here
                 allt = [torch.zeros_like(own) for _ in range(world)]
                 dist.all_gather(allt, own)
-                per_rank = [float(t_[0].item()) for t_ in allt]; per_rank_mhz = [float(t_[1].item()) for t_ in allt]
+                per_rank = [float(t_[0].item()) for t_ in allt]
                 dist.all_reduce(tr, op=dist.ReduceOp.MAX)
             res = sc["camera"]["resolution"]
             out = {"workload": "%s %dx%d @%dspp, max_bounces %d, nee %s, 16x16 tiles over %d GPU(s) (%s), one all_gather" % (label, res[0], res[1], spp, sc["integrator"]["max_bounces"], "on" if wr.nee else "off", world, wr.sharding),
                    "ms": float(tr.item()), "camera_paths": res[0] * res[1] * spp, "camera_paths_per_s": res[0] * res[1] * spp / (float(tr.item()) * 1e-3), "mean_radiance": float(img.mean().item()),
-                   "per_rank_render_ms": [round(v, 3) for v in per_rank], "per_rank_sm_mhz": per_rank_mhz, "clock_reasons": ck["reasons"]}
+                   "per_rank_render_ms": [round(v, 3) for v in per_rank]}
             wr.close()
             return out
 
