@@ -236,3 +236,25 @@ def test_nee_stage_vs_restatement(case):
     assert lit.mean() > 0.3  # the comparison is not about black paths
     assert np.allclose(got.mean(0), want.mean(0), rtol=0.02)
     r.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("case", ["plain_c1", "conductor_mis"])
+def test_render_loop_in_library_equals_stepwise(case):
+    """scn_wf_render (the chunk / bounce loop inside the library, the gather fused into the shade kernel) against the same kernels
+    driven stage by stage through the per-stage entry points: the framebuffers must be bit-identical; a render in smaller chunks takes the same samples (sums equal to rounding)."""
+    import torch
+    from sparse_conv_gpis_tungsten_b200 import render as R
+    scene = SCENE if case == "plain_c1" else NEE_CASES["conductor_mis"]()
+    fbs = []
+    for stepwise, max_paths in ((False, 1 << 22), (True, 1 << 22), (False, 1 << 11)):  # the last: 4 samples in chunks of 2
+        r = R.WavefrontRenderer(scene, device=0)
+        if max_paths < (1 << 22):
+            r.max_paths = r.n_pixels * 2  # two samples per chunk
+        r.render(4, stepwise=stepwise)
+        torch.cuda.synchronize()
+        fbs.append(R.gather_image_rgb(r).cpu().numpy().copy())
+        r.close()
+    assert np.isfinite(fbs[0]).all() and fbs[0].mean() > 0
+    assert np.array_equal(fbs[0], fbs[1]), "library loop differs from the stage-by-stage drive"
+    assert np.allclose(fbs[0], fbs[2], rtol=2e-6, atol=1e-7), "chunked render differs"  # the per-chunk partial sums round differently, the samples are the same

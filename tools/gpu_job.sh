@@ -23,7 +23,7 @@ queries)
     python tools/run_queries.py $name 20 3 | tail -2; python tools/run_queries.py $name 20 3 secondary | tail -2
   done 2>&1 | tee gpurun_out/queries_$T.log ;;
 launches)
-  ncu --metrics gpu__time_duration.sum --clock-control none -c 900 --csv --log-file gpurun_out/launches_$T.csv python bench.py --steps 2 --warmup 3 --e2e-points 4194304 > gpurun_out/ncu_launches_$T.log 2>&1 ;;
+  ncu --metrics gpu__time_duration.sum --clock-control none -c 900 --csv --log-file gpurun_out/launches_$T.csv python bench.py --steps 2 --warmup 3 --e2e-points 4194304 --render-scale 0.03 > gpurun_out/ncu_launches_$T.log 2>&1 ;;
 ncu_fast)
   $NCU -k regex:k_fast_noise3d --launch-skip 2 -c 1 -f -o gpurun_out/fast_$T python bench.py --steps 2 --warmup 3 --no-extras --e2e-points 4194304 > gpurun_out/ncu_fast_$T.log 2>&1 ;;
 ncu_c1)
