@@ -311,6 +311,21 @@ int scn_sample_distance_batch(const scn_medium *m, const scn_rays *rays, const s
                               size_t n, void *stream);
 int scn_sample_distance_batch_host(scn_medium *m, const scn_rays *rays, const scn_state *state, const scn_samples *out, size_t n);
 
+/* NO COUNTERPART IN THE REFERENCE — added for callers that cannot allocate device memory
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).  Same contract and same results as
+ * scn_sample_distance_batch (device buffers, state updated in place), for the media whose query kernel needs per-ray scratch
+ * memory (1D-sampling media, scn_medium_info().query_kernel == SCN_KERNEL_MARCH1D): the 52 bytes of scratch per ray that
+ * scn_sample_distance_batch takes from the medium's stream-ordered pool live here in ONE file-scope device array of
+ * SCN_STATIC_SCRATCH_MAX_RAYS rays (3.25 MiB, held by every GPU that loads the library until the process exits).  The call performs
+ * no cudaMalloc / cudaFree / pool allocation; it enqueues a clear of the part of the array it uses, then the kernels.
+ *   n > SCN_STATIC_SCRATCH_MAX_RAYS        -> SCN_EINVAL (split the wavefront or call scn_sample_distance_batch)
+ *   a medium whose kernel uses no scratch  -> SCN_EUNSUPPORTED (scn_sample_distance_batch allocates nothing for it either)
+ * Every call on a device shares the one array: calls that can overlap on the GPU (different streams, different media, different
+ * host threads) RACE — serialise them on one stream or with events.  The array keeps the previous call's contents between calls. */
+#define SCN_STATIC_SCRATCH_MAX_RAYS 65536
+int scn_sample_distance_batch_static(const scn_medium *m, const scn_rays *rays, const scn_state *state, const scn_samples *out,
+                                     size_t n, void *stream);
+
 /* Medium::transmittance (media/GaussianProcessMedium.cpp:343-393): T_out[i] = 1 (no crossing) or 0 */
 int scn_transmittance_batch(const scn_medium *m, const scn_rays *rays, const scn_state *state, float *T_out, size_t n, void *stream);
 int scn_transmittance_batch_host(scn_medium *m, const scn_rays *rays, const scn_state *state, float *T_out, size_t n);

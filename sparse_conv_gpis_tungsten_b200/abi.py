@@ -92,6 +92,7 @@ class MediumInfo(C.Structure):
                 ("device", C.c_int32), ("sm_count", C.c_int32), ("kernel_radius", C.c_float)]
 
 
+STATIC_SCRATCH_MAX_RAYS = 65536  # SCN_STATIC_SCRATCH_MAX_RAYS (scn_sample_distance_batch_static)
 KERNEL_NAMES = {0: "generic", 1: "k_march", 2: "k_march1d", 3: "k_fast_noise3d"}
 
 # every symbol include/scn.h declares: name -> (restype, argtypes)
@@ -110,6 +111,7 @@ SYMBOLS = {
     "scn_conditioning_batch": (C.c_int, [MediumP, C.POINTER(EvalIn), f32p, f32p, f32p, f32p, C.POINTER(f32p * 7), C.c_size_t, C.c_void_p]),
     "scn_sample_distance_batch": (C.c_int, [MediumP, C.POINTER(Rays), C.POINTER(State), C.POINTER(Samples), C.c_size_t, C.c_void_p]),
     "scn_sample_distance_batch_host": (C.c_int, [MediumP, C.POINTER(Rays), C.POINTER(State), C.POINTER(Samples), C.c_size_t]),
+    "scn_sample_distance_batch_static": (C.c_int, [MediumP, C.POINTER(Rays), C.POINTER(State), C.POINTER(Samples), C.c_size_t, C.c_void_p]),
     "scn_transmittance_batch": (C.c_int, [MediumP, C.POINTER(Rays), C.POINTER(State), f32p, C.c_size_t, C.c_void_p]),
     "scn_transmittance_batch_host": (C.c_int, [MediumP, C.POINTER(Rays), C.POINTER(State), f32p, C.c_size_t]),
     "scn_nee_pdf_batch": (C.c_int, [MediumP, C.POINTER(NeeIn), f32p, C.c_size_t, C.c_void_p]),

@@ -211,6 +211,28 @@ static int launch_march(const scn_medium *m, const Rays &kr, const State &ks, co
     return SCN_OK;
 }
 
+// scn_sample_distance_batch_static: k_march1d's per-ray scratch for callers that may not allocate.  One array per GPU that loads the
+// library, shared by every call on that GPU.  In host code `g_static_scratch1d` is only the symbol's host-side stand-in, never a device
+// address: the address the kernels get comes from cudaGetSymbolAddress, asked once per device with that device current.
+static __device__ __align__(256) unsigned char g_static_scratch1d[SCRATCH1D_BYTES_PER_RAY * (size_t)SCN_STATIC_SCRATCH_MAX_RAYS];
+constexpr int STATIC_SCRATCH_MAX_DEVICES = 64;
+static std::mutex g_static_scratch_mu;
+static void *g_static_scratch_ptr[STATIC_SCRATCH_MAX_DEVICES] = {};
+// the calling thread's current device must be `device`
+static int static_scratch_for(int device, void **out) {
+    if (device < 0 || device >= STATIC_SCRATCH_MAX_DEVICES) return set_error(SCN_EINVAL, "static scratch: device %d beyond the %d this library keeps an address for", device, STATIC_SCRATCH_MAX_DEVICES);
+    std::lock_guard<std::mutex> lk(g_static_scratch_mu);
+    if (!g_static_scratch_ptr[device]) {
+        void *p = nullptr;
+        cudaError_t e = cudaGetSymbolAddress(&p, g_static_scratch1d);
+        if (e != cudaSuccess) return cuda_fail(e, "cudaGetSymbolAddress(static scratch)");
+        if (!p) return set_error(SCN_ECUDA, "cudaGetSymbolAddress returned a null address for the static scratch on device %d", device);
+        g_static_scratch_ptr[device] = p;
+    }
+    *out = g_static_scratch_ptr[device];
+    return SCN_OK;
+}
+
 extern "C" {
 
 const char *scn_last_error(void) { return last_error(); }
@@ -351,6 +373,33 @@ int scn_sample_distance_batch(const scn_medium *m, const scn_rays *rays, const s
     if (use_march(m)) return launch_march<false>(m, kr, ks, ko, nullptr, nullptr, n, (cudaStream_t)stream);
     k_sample_distance<<<grid_for(n), BLOCK, 0, (cudaStream_t)stream>>>(m->P, kr, ks, ko, n);
     return check_launch("k_sample_distance");
+}
+
+// No counterpart in the reference (include/scn.h): k_cond1d -> k_march1d -> k_finish1d over the file-scope scratch array; no allocation.
+int scn_sample_distance_batch_static(const scn_medium *m, const scn_rays *rays, const scn_state *state, const scn_samples *out, size_t n, void *stream) {
+    if (!m || !rays || !state || !out) return set_error(SCN_EINVAL, "null argument");
+    if (!m->march1d) return set_error(SCN_EUNSUPPORTED, "scn_sample_distance_batch_static serves the media whose kernel needs scratch memory (1D sampling, SCN_KERNEL_MARCH1D); "
+                                                        "this medium's kernel uses none: call scn_sample_distance_batch, which allocates nothing for it");
+    if (n > (size_t)SCN_STATIC_SCRATCH_MAX_RAYS) return set_error(SCN_EINVAL, "scn_sample_distance_batch_static: %zu rays exceed the static scratch of SCN_STATIC_SCRATCH_MAX_RAYS = %d rays "
+                                                                  "(split the wavefront or call scn_sample_distance_batch)", n, (int)SCN_STATIC_SCRATCH_MAX_RAYS);
+    if (n == 0) return SCN_OK;
+    if (!out->ok || !out->exited || !out->t || !out->continued_t || !out->gx || !out->gy || !out->gz || !out->gp_id || !out->scheme || !out->weight)
+        return set_error(SCN_EINVAL, "samples: every output but n_evals is required");
+    Rays kr; State ks;
+    if (int rc = to_rays(rays, kr)) return rc;
+    if (int rc = to_state(state, ks)) return rc;
+    DeviceGuard g(m->device); if (!g.ok) return set_error(SCN_ECUDA, "cannot select device %d", m->device);
+    void *scratch = nullptr;
+    if (int rc = static_scratch_for(m->device, &scratch)) return rc;
+    cudaStream_t s = (cudaStream_t)stream;
+    MarchArgs A; A.r = kr; A.s = ks; A.T = nullptr; A.n_evals = nullptr; A.n = (unsigned)n; A.K = march_cache_entries(m->P.n_imp, m->P.iso3d != 0);
+    A.o.ok = out->ok; A.o.exited = out->exited; A.o.t = out->t; A.o.cont_t = out->continued_t; A.o.gx = out->gx; A.o.gy = out->gy; A.o.gz = out->gz;
+    A.o.gp_id = out->gp_id; A.o.scheme = out->scheme; A.o.weight = out->weight; A.o.n_evals = out->n_evals;
+    A.counter = m->counters + (m->next_counter.fetch_add(1) % scn_medium::COUNTERS); // the medium's ring, allocated at scn_medium_create
+    SCN_CUDA(cudaMemsetAsync(A.counter, 0, sizeof(unsigned int), s));
+    cudaError_t e = launch_march1d_sample_on(m->P, A, m->sm_count, scratch, s);
+    if (e != cudaSuccess) return cuda_fail(e, "k_march1d (static scratch)");
+    return SCN_OK;
 }
 
 static int transmittance_impl(const scn_medium *m, const scn_rays *rays, const scn_state *state, float *T, uint32_t *n_evals, size_t n, cudaStream_t s) {

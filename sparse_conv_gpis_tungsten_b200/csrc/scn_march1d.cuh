@@ -414,6 +414,37 @@ inline cudaError_t launch_march1d_t(const Params &P, const MarchArgs &A, int sm_
     return e != cudaSuccess ? e : e2;
 }
 
+// The same three launches over scratch the CALLER of this function owns (scn_sample_distance_batch_static: a file-scope device array,
+// scn_api.cu): nothing is allocated or freed here.  `scratch` is a DEVICE address of at least SCRATCH1D_BYTES_PER_RAY * A.n bytes; the part
+// in use is cleared in-stream first (the array outlives the call and still holds the previous wavefront's flags and coefficients).
+inline cudaError_t launch_march1d_sample_on(const Params &P, const MarchArgs &A, int sm_count, void *scratch, cudaStream_t s) {
+    cudaError_t e = cudaMemsetAsync(scratch, 0, SCRATCH1D_BYTES_PER_RAY * (size_t)A.n, s);
+    if (e != cudaSuccess) return e;
+    const Scratch1D X = scratch1d_carve(scratch, A.n);
+    const unsigned per_ray_grid = (A.n + MARCH1D_BLOCK - 1) / MARCH1D_BLOCK;
+    if (P.activate_conditioning) k_cond1d<<<per_ray_grid, MARCH1D_BLOCK, 0, s>>>(P, A.r, A.s, X, A.n);
+    const int var = P.multires ? 2 : (P.stationary ? 0 : 1);
+    auto launch = [&](auto kern) -> cudaError_t {
+        int per_sm = 0;
+        cudaError_t er = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, MARCH1D_BLOCK, 0);
+        if (er != cudaSuccess) return er;
+        unsigned grid = (unsigned)(sm_count * (per_sm < 1 ? 1 : per_sm)); if (grid > per_ray_grid) grid = per_ray_grid;
+        kern<<<grid, MARCH1D_BLOCK, 0, s>>>(P, A, X);
+        return cudaSuccess;
+    };
+#define SCN_M1D(N) (var == 2 ? launch(k_march1d<false, N, 2>) : (var == 1 ? launch(k_march1d<false, N, 1>) : launch(k_march1d<false, N, 0>)))
+    switch (P.n_imp) {
+    case 1: e = SCN_M1D(1); break;
+    case 2: e = SCN_M1D(2); break;
+    case 3: e = SCN_M1D(3); break;
+    default: e = SCN_M1D(4); break;
+    }
+#undef SCN_M1D
+    if (e != cudaSuccess) return e;
+    k_finish1d<<<per_ray_grid, MARCH1D_BLOCK, 0, s>>>(P, A, X);
+    return cudaGetLastError();
+}
+
 #endif // __CUDACC__
 
 } // namespace scn

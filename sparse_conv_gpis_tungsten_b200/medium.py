@@ -312,6 +312,23 @@ class SparseConvolutionNoiseMedium:
             abi.check(self._lib.scn_sample_distance_batch_host(self._h, C.byref(r), C.byref(s), C.byref(o), a.n))
         return out
 
+    def sample_distance_static(self, rays, state, out, scene_seed=0, stream=None):
+        """scn_sample_distance_batch_static (no counterpart in the reference): sample_distance for 1D-sampling media over the library's
+        file-scope scratch array — device buffers only, every output buffer supplied by the caller (nothing is allocated here or in the
+        library), at most abi.STATIC_SCRATCH_MAX_RAYS rays, and calls that overlap on the GPU race."""
+        a = _Args()
+        r = self._rays(a, rays, scene_seed)
+        s = self._state(a, state)
+        o = abi.Samples()
+        for k, dt in SAMPLE_FIELDS:
+            setattr(o, k, a.ptr(out[k], dt, k))
+        if out.get("n_evals") is not None:
+            o.n_evals = a.ptr(out["n_evals"], np.uint32, "n_evals")
+        if not a.on_device:
+            raise ValueError("sample_distance_static takes device buffers only")
+        abi.check(self._lib.scn_sample_distance_batch_static(self._h, C.byref(r), C.byref(s), C.byref(o), a.n, _stream_ptr(stream)))
+        return out
+
     def transmittance(self, rays, state, scene_seed=0, out=None, stream=None):
         """Medium::transmittance for a wavefront (GaussianProcessMedium.cpp:343-393): 1 where the ray exits uncrossed, else 0."""
         a = _Args()
