@@ -230,7 +230,8 @@ def test_medium_info_reports_the_kernel_family(torch_cuda):
     """scn_medium_info: a configuration that falls to the generic one-thread-per-ray kernels is visible through the API."""
     from sparse_conv_gpis_tungsten_b200 import SparseConvolutionNoiseMedium
     want = {"c1_sphere_3d_none": "k_march", "c5_multires_nonstat_renewalplus": "k_march", "world_3d_renewalplus": "k_march", "c3_1d_renewal": "k_march1d",
-            "multires_1d_xy": "k_march1d", "matern15_world": "generic"}
+            "multires_1d_xy": "k_march1d", "matern15_world": "generic", "proc_mean_knob_iso": "k_march", "proc_mean_plane_world": "k_march",
+            "proc_mean_grid_sdf_iso": "k_march", "proc_mean_knob_inner_1d": "generic"}
     for name, kern in want.items():
         m = SparseConvolutionNoiseMedium.from_json(S.MEDIA[name])
         i = m.info()
@@ -244,7 +245,8 @@ def test_medium_info_reports_the_kernel_family(torch_cuda):
     assert SparseConvolutionNoiseMedium.from_json(S.microbench_medium(3, True)).info()["eval_kernel"] == "k_fast_noise3d"
 
 
-@pytest.mark.parametrize("name", ["c1_sphere_3d_none", "c5_multires_nonstat_renewalplus", "c3_1d_renewal", "world_3d_renewalplus"])
+@pytest.mark.parametrize("name", ["c1_sphere_3d_none", "c5_multires_nonstat_renewalplus", "c3_1d_renewal", "world_3d_renewalplus",
+                                  "proc_mean_knob_iso", "proc_mean_plane_world", "proc_mean_grid_sdf_iso", "proc_mean_two_spheres_iso", "proc_mean_knob_outer_world"])
 def test_tuned_kernels_equal_generic_kernels(torch_cuda, name):
     """The tuned query kernels (k_march, k_march1d) against the generic one-thread-per-ray walk of the same library on 4096 secondary
     rays: same decisions, 1e-4 on matched queries (both are held to the reference separately; this pins them to each other)."""
@@ -253,5 +255,6 @@ def test_tuned_kernels_equal_generic_kernels(torch_cuda, name):
     generic.m.force_generic(True)
     a, b = tuned.sample_distance(rays, st, 4), generic.sample_distance(rays, st, 4)
     r = S.query_parity_rates(a, b, tuned.transmittance(rays, st, 4), generic.transmittance(rays, st, 4))
-    assert r["decision"] + r["step_moved"] <= 3 and r["t_rel_max"] <= TOL and r["grad_rel_p999"] <= TOL and r["transmittance_mismatch"] <= 2, r
+    gtol = G.grad_tol(name)  # procedural means: the gradient is a forward difference of the SDF (eps 1e-3), which amplifies the rounding of the hit point
+    assert r["decision"] + r["step_moved"] <= 3 and r["t_rel_max"] <= TOL and r["grad_rel_p999"] <= gtol and r["transmittance_mismatch"] <= 2, r
     tuned.close(); generic.close()

@@ -1,7 +1,7 @@
 """Developer tool: run the medium-query kernels on a seeded wavefront and print queries/s and noise evals/s
 (CUDA events).  Used as the short command for `ncu` captures of the march kernels.
 
-  python tools/run_queries.py [medium-name] [log2 rays] [repeats] [primary|secondary]
+  python tools/run_queries.py [medium-name] [log2 rays] [repeats] [primary|secondary] [generic]
 """
 import os
 import sys
@@ -18,6 +18,9 @@ reps = int(sys.argv[3]) if len(sys.argv) > 3 else 3
 secondary = len(sys.argv) > 4 and sys.argv[4] == "secondary"
 
 g = S.GpuImpl(S.MEDIA[name])
+if "generic" in sys.argv[4:]:
+    g.m.force_generic(True)  # the one-thread-per-ray kernels, for before / after rates
+print(name, g.m.info()["query_kernel"], flush=True)
 rays, st = S.camera_rays(n, seed=11, secondary=secondary)
 stream = torch.cuda.current_stream()
 out = None
