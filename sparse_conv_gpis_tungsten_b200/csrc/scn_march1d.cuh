@@ -20,7 +20,7 @@
 //
 // Covered: 1D sampling with the stationary squared-exponential kernel and with its brute-force non-stationary form (BRUTE: kernel scale,
 // variance normalisation and conditioning scale follow ls(p) at the query point) and its multi-resolution form (two levels, each with its
-// own register window), 1 <= N <= 4 (compile-time).
+// own register window), 1 <= N <= 4 (compile-time), every mean (procedural means through the PROC instantiations).
 // Everything else stays on the generic kernels of scn_api.cu.
 #ifndef SCN_MARCH1D_CUH_
 #define SCN_MARCH1D_CUH_
@@ -30,7 +30,7 @@
 namespace scn {
 
 inline bool march1d_supported(const Params &P) {
-    return P.sampling_1d && !P.use_mtx && !P.has_aniso && P.kernel == SCN_COV_SQUARED_EXPONENTIAL && P.n_imp >= 1 && P.n_imp <= 4 && !has_procedural_mean(P);
+    return P.sampling_1d && !P.use_mtx && !P.has_aniso && P.kernel == SCN_COV_SQUARED_EXPONENTIAL && P.n_imp >= 1 && P.n_imp <= 4;
 }
 
 #if defined(__CUDACC__)
@@ -162,7 +162,8 @@ __global__ void __launch_bounds__(MARCH1D_BLOCK) k_cond1d(const __grid_constant_
 }
 
 // VAR: 0 = stationary kernel, 1 = brute-force non-stationary (point-dependent kernel scale), 2 = multi-resolution (two levels, SCN:126-135)
-template <bool TRANSMIT, int NIMP, int VAR>
+// PROC: the instantiation carries the procedural means (proc_mean: SDF functions, a field behind the mean); the media without one keep it compiled out
+template <bool TRANSMIT, int NIMP, int VAR, bool PROC = false>
 // resident blocks per SM the register allocation must allow: 5 (<= 102 registers) for stationary media, 4 / 3 for the brute-force and
 // multi-resolution variants; the calls into the procedural-field code (cold for most media) then spill around the call instead of
 // raising the whole kernel's register count
@@ -296,7 +297,7 @@ __global__ void __launch_bounds__(MARCH1D_BLOCK, VAR == 0 ? 5 : (VAR == 1 ? 4 : 
         }
         if (active) {
             const float amp = VAR == 0 ? P.sigma : cov_amplitude(P, p); // stationary instantiations carry no procedural-field code
-            double mean; gp_mean_and_id<false>(P, p, mean, id);
+            double mean; gp_mean_and_id<PROC>(P, p, mean, id);
             if (P.surf_vol_sep) id = 1.f < P.surf_vol_thresh ? 0 : 1;
             fval = (float)yadd((double)xmul(amp, nv), mean);
         }
@@ -391,6 +392,7 @@ inline cudaError_t launch_march1d_t(const Params &P, const MarchArgs &A, int sm_
     const unsigned per_ray_grid = (A.n + MARCH1D_BLOCK - 1) / MARCH1D_BLOCK;
     if (P.activate_conditioning) k_cond1d<<<per_ray_grid, MARCH1D_BLOCK, 0, s>>>(P, A.r, A.s, X, A.n);
     const int var = P.multires ? 2 : (P.stationary ? 0 : 1);
+    const bool proc = has_procedural_mean(P);
     auto launch = [&](auto kern) -> cudaError_t {
         int per_sm = 0; // resident blocks per SM (registers): one wave of persistent blocks
         cudaError_t er = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, MARCH1D_BLOCK, 0);
@@ -399,7 +401,8 @@ inline cudaError_t launch_march1d_t(const Params &P, const MarchArgs &A, int sm_
         kern<<<grid, MARCH1D_BLOCK, 0, s>>>(P, A, X);
         return cudaSuccess;
     };
-#define SCN_M1D(N) (var == 2 ? launch(k_march1d<TRANSMIT, N, 2>) : (var == 1 ? launch(k_march1d<TRANSMIT, N, 1>) : launch(k_march1d<TRANSMIT, N, 0>)))
+#define SCN_M1D_P(N, PR) (var == 2 ? launch(k_march1d<TRANSMIT, N, 2, PR>) : (var == 1 ? launch(k_march1d<TRANSMIT, N, 1, PR>) : launch(k_march1d<TRANSMIT, N, 0, PR>)))
+#define SCN_M1D(N) (proc ? SCN_M1D_P(N, true) : SCN_M1D_P(N, false))
     switch (P.n_imp) {
     case 1: e = SCN_M1D(1); break;
     case 2: e = SCN_M1D(2); break;
@@ -407,6 +410,7 @@ inline cudaError_t launch_march1d_t(const Params &P, const MarchArgs &A, int sm_
     default: e = SCN_M1D(4); break;
     }
 #undef SCN_M1D
+#undef SCN_M1D_P
     if (e != cudaSuccess) { cudaFreeAsync(scratch, s); return e; }
     if (!TRANSMIT) k_finish1d<<<per_ray_grid, MARCH1D_BLOCK, 0, s>>>(P, A, X);
     e = cudaGetLastError();
@@ -424,6 +428,7 @@ inline cudaError_t launch_march1d_sample_on(const Params &P, const MarchArgs &A,
     const unsigned per_ray_grid = (A.n + MARCH1D_BLOCK - 1) / MARCH1D_BLOCK;
     if (P.activate_conditioning) k_cond1d<<<per_ray_grid, MARCH1D_BLOCK, 0, s>>>(P, A.r, A.s, X, A.n);
     const int var = P.multires ? 2 : (P.stationary ? 0 : 1);
+    const bool proc = has_procedural_mean(P);
     auto launch = [&](auto kern) -> cudaError_t {
         int per_sm = 0;
         cudaError_t er = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, MARCH1D_BLOCK, 0);
@@ -432,7 +437,8 @@ inline cudaError_t launch_march1d_sample_on(const Params &P, const MarchArgs &A,
         kern<<<grid, MARCH1D_BLOCK, 0, s>>>(P, A, X);
         return cudaSuccess;
     };
-#define SCN_M1D(N) (var == 2 ? launch(k_march1d<false, N, 2>) : (var == 1 ? launch(k_march1d<false, N, 1>) : launch(k_march1d<false, N, 0>)))
+#define SCN_M1D_P(N, PR) (var == 2 ? launch(k_march1d<false, N, 2, PR>) : (var == 1 ? launch(k_march1d<false, N, 1, PR>) : launch(k_march1d<false, N, 0, PR>)))
+#define SCN_M1D(N) (proc ? SCN_M1D_P(N, true) : SCN_M1D_P(N, false))
     switch (P.n_imp) {
     case 1: e = SCN_M1D(1); break;
     case 2: e = SCN_M1D(2); break;
@@ -440,6 +446,7 @@ inline cudaError_t launch_march1d_sample_on(const Params &P, const MarchArgs &A,
     default: e = SCN_M1D(4); break;
     }
 #undef SCN_M1D
+#undef SCN_M1D_P
     if (e != cudaSuccess) return e;
     k_finish1d<<<per_ray_grid, MARCH1D_BLOCK, 0, s>>>(P, A, X);
     return cudaGetLastError();
