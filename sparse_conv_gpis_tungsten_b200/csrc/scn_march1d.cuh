@@ -30,7 +30,7 @@
 namespace scn {
 
 inline bool march1d_supported(const Params &P) {
-    return P.sampling_1d && !P.use_mtx && !P.has_aniso && P.kernel == SCN_COV_SQUARED_EXPONENTIAL && P.n_imp >= 1 && P.n_imp <= 4;
+    return P.sampling_1d && !P.has_aniso && P.kernel == SCN_COV_SQUARED_EXPONENTIAL && P.n_imp >= 1 && P.n_imp <= 4;
 }
 
 #if defined(__CUDACC__)
@@ -162,7 +162,8 @@ __global__ void __launch_bounds__(MARCH1D_BLOCK) k_cond1d(const __grid_constant_
 }
 
 // VAR: 0 = stationary kernel, 1 = brute-force non-stationary (point-dependent kernel scale), 2 = multi-resolution (two levels, SCN:126-135)
-// PROC: the instantiation carries the procedural means (proc_mean: SDF functions, a field behind the mean); the media without one keep it compiled out
+// PROC: the instantiation carries the procedural means (proc_mean: SDF functions, a field behind the mean) and the full anisotropy matrix
+// ("useAnisoMtx"); the media without either keep that code compiled out
 template <bool TRANSMIT, int NIMP, int VAR, bool PROC = false>
 // resident blocks per SM the register allocation must allow: 5 (<= 102 registers) for stationary media, 4 / 3 for the brute-force and
 // multi-resolution variants; the calls into the procedural-field code (cold for most media) then spill around the call instead of
@@ -170,6 +171,8 @@ template <bool TRANSMIT, int NIMP, int VAR, bool PROC = false>
 __global__ void __launch_bounds__(MARCH1D_BLOCK, VAR == 0 ? 5 : (VAR == 1 ? 4 : 3)) k_march1d(const __grid_constant__ Params P, const MarchArgs A, const Scratch1D X) {
     const unsigned FULL = 0xffffffffu;
     const int lane = threadIdx.x & 31;
+    // world -> the kernel's local frame: the anisotropy scales, or the full matrix of "useAnisoMtx" (PROC instantiations only)
+    auto w2l = [&](const f3 v) -> f3 { return (PROC && P.use_mtx) ? mtx_mulv(P.mW, v) : xmul3(l_inv(P), v); };
     const unsigned lt = (1u << lane) - 1u;
     const bool absorb = !TRANSMIT && P.absorption_only;
     const bool cond_on = P.activate_conditioning != 0;
@@ -245,7 +248,7 @@ __global__ void __launch_bounds__(MARCH1D_BLOCK, VAR == 0 ? 5 : (VAR == 1 ? 4 : 
                         if (conditioned) { // coefficients from k_cond1d; o_ray of evaluateNoise1DNormalized is constant along the ray
                             cvs = X.c[0][ri]; cgz = X.c[3][ri];
                             corg = F3(X.c[4][ri], X.c[5][ri], X.c[6][ri]);
-                            oz = xdot(fr.n, BRUTE ? cov_pos_w2l(P, corg, 1.0f) : xmul3(l_inv(P), corg));
+                            oz = xdot(fr.n, BRUTE ? cov_pos_w2l(P, corg, 1.0f) : w2l(corg));
                             if (MULTI) { const Levels oi = level_ratio(P, corg); osf_lo = oi.r_lo; osf_hi = oi.r_hi; }
                             evals = P.ctx == SCN_CTX_RENEWAL_PLUS ? 2u : 1u;
                         }
@@ -277,7 +280,7 @@ __global__ void __launch_bounds__(MARCH1D_BLOCK, VAR == 0 ? 5 : (VAR == 1 ? 4 : 
             // transformPosDirWorldtoLocal (GPF:631-633; stationary: the division by 1 is exact; BRUTE: max ls; MULTI: the level's scale), z of the ray frame
             float z = 0.f, frac = 0.f; int i = 0;
             if (active) {
-                z = xdot(frn, MULTI ? xdiv3(xmul3(l_inv(P), p), kss) : (BRUTE ? cov_pos_w2l(P, p, 1.0f) : xmul3(l_inv(P), p)));
+                z = xdot(frn, MULTI ? xdiv3(w2l(p), kss) : (BRUTE ? cov_pos_w2l(P, p, 1.0f) : w2l(p)));
                 const float tg = xdiv(z, R), fl = floorf(tg);
                 frac = xsub(tg, fl); i = (int)fl;
             }
@@ -286,7 +289,7 @@ __global__ void __launch_bounds__(MARCH1D_BLOCK, VAR == 0 ? 5 : (VAR == 1 ? 4 : 
             if (active) {
                 nl = sv / (BRUTE ? sqrtf(se_variance1d(P, R, lsq)) : nf); // SCN:334-336
                 if (conditioned) { // SCN:338-357
-                    const float ozl = MULTI ? xdot(frn, xdiv3(xmul3(l_inv(P), corg), kss)) : oz;
+                    const float ozl = MULTI ? xdot(frn, xdiv3(w2l(corg), kss)) : oz;
                     const float ab = z - ozl;
                     const float cls = BRUTE ? cov_splat_cov1d(P, p, corg) : 1.0f;
                     const float osf = MULTI ? (l ? osf_hi : osf_lo) : 1.0f;
@@ -392,7 +395,7 @@ inline cudaError_t launch_march1d_t(const Params &P, const MarchArgs &A, int sm_
     const unsigned per_ray_grid = (A.n + MARCH1D_BLOCK - 1) / MARCH1D_BLOCK;
     if (P.activate_conditioning) k_cond1d<<<per_ray_grid, MARCH1D_BLOCK, 0, s>>>(P, A.r, A.s, X, A.n);
     const int var = P.multires ? 2 : (P.stationary ? 0 : 1);
-    const bool proc = has_procedural_mean(P);
+    const bool proc = has_procedural_mean(P) || P.use_mtx;
     auto launch = [&](auto kern) -> cudaError_t {
         int per_sm = 0; // resident blocks per SM (registers): one wave of persistent blocks
         cudaError_t er = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, MARCH1D_BLOCK, 0);
@@ -428,7 +431,7 @@ inline cudaError_t launch_march1d_sample_on(const Params &P, const MarchArgs &A,
     const unsigned per_ray_grid = (A.n + MARCH1D_BLOCK - 1) / MARCH1D_BLOCK;
     if (P.activate_conditioning) k_cond1d<<<per_ray_grid, MARCH1D_BLOCK, 0, s>>>(P, A.r, A.s, X, A.n);
     const int var = P.multires ? 2 : (P.stationary ? 0 : 1);
-    const bool proc = has_procedural_mean(P);
+    const bool proc = has_procedural_mean(P) || P.use_mtx;
     auto launch = [&](auto kern) -> cudaError_t {
         int per_sm = 0;
         cudaError_t er = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, MARCH1D_BLOCK, 0);
