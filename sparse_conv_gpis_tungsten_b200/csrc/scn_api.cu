@@ -203,7 +203,7 @@ static bool use_march(const scn_medium *m) { return (m->march_block != 0 || m->m
 constexpr size_t MAX_WAVEFRONT = 0x40000000u; // the persistent kernels' ray counter is 32 bits wide
 template <bool TRANSMIT>
 static int launch_march(const scn_medium *m, const Rays &kr, const State &ks, const Samples &ko, float *T, uint32_t *n_evals, size_t n, cudaStream_t s) {
-    MarchArgs A; A.r = kr; A.s = ks; A.o = ko; A.T = T; A.n_evals = n_evals; A.n = (unsigned)n; A.K = march_cache_entries(m->P.n_imp, m->P.iso3d != 0);
+    MarchArgs A; A.r = kr; A.s = ks; A.o = ko; A.T = T; A.n_evals = n_evals; A.n = (unsigned)n; A.K = march_cache_entries(m->P.n_imp, march_rayz(m->P));
     A.counter = m->counters + (m->next_counter.fetch_add(1) % scn_medium::COUNTERS);
     SCN_CUDA(cudaMemsetAsync(A.counter, 0, sizeof(unsigned int), s));
     cudaError_t e = m->march1d ? launch_march1d_t<TRANSMIT>(m->P, A, m->sm_count, m->pool, s) : launch_march_t<TRANSMIT>(m->P, A, m->march_block, m->sm_count, s);
@@ -392,7 +392,7 @@ int scn_sample_distance_batch_static(const scn_medium *m, const scn_rays *rays, 
     void *scratch = nullptr;
     if (int rc = static_scratch_for(m->device, &scratch)) return rc;
     cudaStream_t s = (cudaStream_t)stream;
-    MarchArgs A; A.r = kr; A.s = ks; A.T = nullptr; A.n_evals = nullptr; A.n = (unsigned)n; A.K = march_cache_entries(m->P.n_imp, m->P.iso3d != 0);
+    MarchArgs A; A.r = kr; A.s = ks; A.T = nullptr; A.n_evals = nullptr; A.n = (unsigned)n; A.K = march_cache_entries(m->P.n_imp, march_rayz(m->P));
     A.o.ok = out->ok; A.o.exited = out->exited; A.o.t = out->t; A.o.cont_t = out->continued_t; A.o.gx = out->gx; A.o.gy = out->gy; A.o.gz = out->gz;
     A.o.gp_id = out->gp_id; A.o.scheme = out->scheme; A.o.weight = out->weight; A.o.n_evals = out->n_evals;
     A.counter = m->counters + (m->next_counter.fetch_add(1) % scn_medium::COUNTERS); // the medium's ring, allocated at scn_medium_create
@@ -469,7 +469,7 @@ int scn_medium_info(const scn_medium *m, scn_medium_info_t *out) {
     out->query_kernel = !tuned ? SCN_KERNEL_GENERIC : (m->march1d ? SCN_KERNEL_MARCH1D : SCN_KERNEL_MARCH3D);
     out->eval_kernel = fast_noise3d_supported(m->P) ? SCN_KERNEL_FAST_NOISE3D : SCN_KERNEL_GENERIC;
     out->march_block = m->march1d ? MARCH1D_BLOCK : m->march_block;
-    out->cache_entries = m->march_block ? march_cache_entries(m->P.n_imp, m->P.iso3d != 0) : 0;
+    out->cache_entries = m->march_block ? march_cache_entries(m->P.n_imp, march_rayz(m->P)) : 0;
     out->smem_bytes = m->march_block ? (uint32_t)march_smem_total(m->P, out->cache_entries, m->march_block) : 0;
     out->device = m->device; out->sm_count = m->sm_count;
     out->kernel_radius = m->P.iso3d || m->P.sampling_1d ? m->P.R_iso : m->P.R_world;
