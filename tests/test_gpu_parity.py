@@ -230,12 +230,14 @@ def test_medium_info_reports_the_kernel_family(torch_cuda):
     """scn_medium_info: a configuration that falls to the generic one-thread-per-ray kernels is visible through the API."""
     from sparse_conv_gpis_tungsten_b200 import SparseConvolutionNoiseMedium
     want = {"c1_sphere_3d_none": "k_march", "c5_multires_nonstat_renewalplus": "k_march", "world_3d_renewalplus": "k_march", "c3_1d_renewal": "k_march1d",
-            "multires_1d_xy": "k_march1d", "matern15_world": "generic", "proc_mean_knob_iso": "k_march", "proc_mean_plane_world": "k_march",
+            "multires_1d_xy": "k_march1d", "matern15_world": "k_march", "gabor_iso_world": "k_march", "proc_mean_knob_iso": "k_march", "proc_mean_plane_world": "k_march",
             "proc_mean_grid_sdf_iso": "k_march", "proc_mean_knob_inner_1d": "k_march1d",
             "aniso_mtx_world_renewalplus": "k_march", "aniso_mtx_iso_renewalplus": "k_march", "aniso_mtx_1d_xy_mis": "k_march1d",
             "aniso_rot_world_bruteforce": "k_march", "aniso_rot_iso_multires": "k_march", "aniso_rot_iso_const_none": "k_march", "grid_aniso_var_world": "k_march"}
+    media = dict(S.MEDIA, one_d_density6=S.microbench_medium(6, True, one_d=True))  # 1D sampling with N > 4: the register window holds at most 4 impulses per cell
+    want["one_d_density6"] = "generic"
     for name, kern in want.items():
-        m = SparseConvolutionNoiseMedium.from_json(S.MEDIA[name])
+        m = SparseConvolutionNoiseMedium.from_json(media[name])
         i = m.info()
         assert i["query_kernel"] == kern, (name, i)
         assert i["sm_count"] > 0 and i["kernel_radius"] > 0
@@ -250,7 +252,8 @@ def test_medium_info_reports_the_kernel_family(torch_cuda):
 @pytest.mark.parametrize("name", ["c1_sphere_3d_none", "c5_multires_nonstat_renewalplus", "c3_1d_renewal", "world_3d_renewalplus",
                                   "proc_mean_knob_iso", "proc_mean_plane_world", "proc_mean_grid_sdf_iso", "proc_mean_two_spheres_iso", "proc_mean_knob_outer_world", "proc_mean_knob_inner_1d",
                                   "aniso_mtx_world_renewalplus", "aniso_mtx_1d_xy_mis", "aniso_mtx_iso_renewalplus",
-                                  "aniso_rot_world_bruteforce", "aniso_rot_iso_multires", "aniso_rot_iso_const_none", "aniso_rot_world_multires_renewal", "grid_aniso_var_world"])
+                                  "aniso_rot_world_bruteforce", "aniso_rot_iso_multires", "aniso_rot_iso_const_none", "aniso_rot_world_multires_renewal", "grid_aniso_var_world",
+                                  "matern05_world", "matern15_world", "matern25_world_global", "gabor_aniso_world", "gabor_iso_world"])
 def test_tuned_kernels_equal_generic_kernels(torch_cuda, name):
     """The tuned query kernels (k_march, k_march1d) against the generic one-thread-per-ray walk of the same library on 4096 secondary
     rays: same decisions, 1e-4 on matched queries (both are held to the reference separately; this pins them to each other)."""
