@@ -206,7 +206,8 @@ static int launch_march(const scn_medium *m, const Rays &kr, const State &ks, co
     MarchArgs A; A.r = kr; A.s = ks; A.o = ko; A.T = T; A.n_evals = n_evals; A.n = (unsigned)n; A.K = march_cache_entries(m->P.n_imp, march_rayz(m->P));
     A.counter = m->counters + (m->next_counter.fetch_add(1) % scn_medium::COUNTERS);
     SCN_CUDA(cudaMemsetAsync(A.counter, 0, sizeof(unsigned int), s));
-    cudaError_t e = m->march1d ? launch_march1d_t<TRANSMIT>(m->P, A, m->sm_count, m->pool, s) : launch_march_t<TRANSMIT>(m->P, A, m->march_block, m->sm_count, s);
+    cudaError_t e = m->march1d ? (TRANSMIT ? march1d_launch_transmit(m->P, A, m->sm_count, m->pool, s) : march1d_launch_sample(m->P, A, m->sm_count, m->pool, s))
+                               : (TRANSMIT ? march_launch_transmit(m->P, A, m->march_block, m->sm_count, s) : march_launch_sample(m->P, A, m->march_block, m->sm_count, s));
     if (e != cudaSuccess) return cuda_fail(e, m->march1d ? "k_march1d" : "k_march");
     return SCN_OK;
 }
@@ -397,7 +398,7 @@ int scn_sample_distance_batch_static(const scn_medium *m, const scn_rays *rays, 
     A.o.gp_id = out->gp_id; A.o.scheme = out->scheme; A.o.weight = out->weight; A.o.n_evals = out->n_evals;
     A.counter = m->counters + (m->next_counter.fetch_add(1) % scn_medium::COUNTERS); // the medium's ring, allocated at scn_medium_create
     SCN_CUDA(cudaMemsetAsync(A.counter, 0, sizeof(unsigned int), s));
-    cudaError_t e = launch_march1d_sample_on(m->P, A, m->sm_count, scratch, s);
+    cudaError_t e = march1d_launch_sample_static(m->P, A, m->sm_count, scratch, s);
     if (e != cudaSuccess) return cuda_fail(e, "k_march1d (static scratch)");
     return SCN_OK;
 }
@@ -445,10 +446,14 @@ int scn_nee_grad_batch(const scn_medium *m, const scn_nee_in *in, float *gx, flo
 // kernels (scn_device.cuh: SCN_CHECK), read and cleared.  The product build answers SCN_EUNSUPPORTED.
 int scn_debug_bounds_failures(unsigned long long out[8]) {
 #if defined(SCN_DEBUG_BOUNDS)
+    // the counters are per translation unit (static __device__): this unit's, then the three units that hold the tuned kernels
     cudaError_t e = cudaMemcpyFromSymbol(out, g_scn_bounds_fail, 8 * sizeof(unsigned long long));
     if (e != cudaSuccess) return cuda_fail(e, "scn_debug_bounds_failures");
     unsigned long long z[8] = {0};
     e = cudaMemcpyToSymbol(g_scn_bounds_fail, z, sizeof z);
+    if (e == cudaSuccess) e = bounds_collect_march_sample(out);
+    if (e == cudaSuccess) e = bounds_collect_march_transmit(out);
+    if (e == cudaSuccess) e = bounds_collect_march1d(out);
     return e == cudaSuccess ? SCN_OK : cuda_fail(e, "scn_debug_bounds_failures");
 #else
     (void)out; return set_error(SCN_EUNSUPPORTED, "built without SCN_DEBUG_BOUNDS");

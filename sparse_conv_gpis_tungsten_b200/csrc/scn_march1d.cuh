@@ -36,6 +36,9 @@ inline bool march1d_supported(const Params &P) {
 #if defined(__CUDACC__)
 
 constexpr int MARCH1D_BLOCK = 128;
+constexpr size_t SCRATCH1D_BYTES_PER_RAY = 13 * sizeof(float); // Scratch1D below: 13 arrays of 4 bytes per ray
+
+#if defined(SCN_MARCH1D_IMPL) // the kernels and their launchers: scn_march1d.cu only (scn_api.cu takes the declarations at the end)
 
 // the 2 + 2 N draws of cell1D (SCN:408-428) for cell index `cell`: positions and a sign bit per impulse (1 = +1)
 template <int NIMP>
@@ -134,7 +137,6 @@ struct Scratch1D {
     uint32_t *evals;
     int32_t *gp_id;       // gp id at the hit: the full int32 of the JSON "id", as the generic and 3D kernels carry it
 };
-constexpr size_t SCRATCH1D_BYTES_PER_RAY = 13 * sizeof(float);
 inline Scratch1D scratch1d_carve(void *base, size_t n) {
     Scratch1D X; float *f = (float *)base;
     for (int j = 0; j < 7; ++j) X.c[j] = f + (size_t)j * n;
@@ -454,6 +456,13 @@ inline cudaError_t launch_march1d_sample_on(const Params &P, const MarchArgs &A,
     k_finish1d<<<per_ray_grid, MARCH1D_BLOCK, 0, s>>>(P, A, X);
     return cudaGetLastError();
 }
+
+#endif // SCN_MARCH1D_IMPL
+
+// instantiated in scn_march1d.cu (a translation unit of its own); scn_api.cu calls these
+cudaError_t march1d_launch_sample(const Params &P, const MarchArgs &A, int sm_count, cudaMemPool_t pool, cudaStream_t s);
+cudaError_t march1d_launch_transmit(const Params &P, const MarchArgs &A, int sm_count, cudaMemPool_t pool, cudaStream_t s);
+cudaError_t march1d_launch_sample_static(const Params &P, const MarchArgs &A, int sm_count, void *scratch, cudaStream_t s);
 
 #endif // __CUDACC__
 

@@ -51,11 +51,7 @@ if __name__ == "__main__":
         worker(sys.argv[3], sys.argv[4]); sys.exit(0)
     out_dir = os.path.join(ROOT, "gpurun_out"); os.makedirs(out_dir, exist_ok=True)
     dbg = os.path.join(out_dir, "libscn_b200_dbg.so")
-    srcs = [os.path.join(build.CSRC, s) for s in build.SOURCES]
-    cmd = [build._nvcc()] + build.NVCC_FLAGS + ["-DSCN_DEBUG_BOUNDS", "-o", dbg] + srcs
-    r = subprocess.run(cmd, capture_output=True, text=True)
-    if r.returncode != 0:
-        print(r.stderr); sys.exit(1)
+    build.compile_and_link(dbg, os.path.join(out_dir, "dbg_obj"), extra_flags=["-DSCN_DEBUG_BOUNDS"])
     outs = []
     for tag, lib in (("product", abi.LIB_PATH), ("debug", dbg)):
         o = os.path.join(out_dir, "debug_bounds_%s.npz" % tag)
