@@ -19,7 +19,10 @@ from sparse_conv_gpis_tungsten_b200 import abi, build
 
 n = 1 << (int(sys.argv[1]) if len(sys.argv) > 1 else 16)
 MEDIA = ["c1_sphere_3d_none", "c5_multires_nonstat_renewalplus", "nonstat_bruteforce_iso", "world_3d_renewalplus", "multires_world", "aniso_mtx_iso_renewalplus",
-         "grid_ls_multires_iso", "c3_1d_renewal", "c4_1d_renewalplus_xy_mis", "multires_1d_xy", "nonstat_bruteforce_1d_renewalplus"]
+         "grid_ls_multires_iso", "c3_1d_renewal", "c4_1d_renewalplus_xy_mis", "multires_1d_xy", "nonstat_bruteforce_1d_renewalplus",
+         # the kernel variants added late in round 2: full-matrix kernels (MODE 3 / 4), Matern / Gabor (MODE 5), procedural means, 1D with the matrix
+         "aniso_mtx_world_renewalplus", "aniso_rot_world_bruteforce", "aniso_rot_iso_multires", "aniso_rot_iso_const_none", "matern15_world", "gabor_aniso_world",
+         "proc_mean_knob_iso", "proc_mean_plane_world", "proc_mean_knob_inner_1d", "aniso_mtx_1d_xy_mis"]
 
 
 def worker(lib_path, out_path):
