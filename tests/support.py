@@ -541,7 +541,10 @@ PARITY_MEDIA = ["c1_sphere_3d_none", "c3_1d_renewal", "c4_1d_renewalplus_xy_mis"
                 "world_3d_renewalplus", "multires_world", "nonstat_bruteforce_iso", "nonstat_bruteforce_world_var", "nonstat_bruteforce_1d_renewalplus",
                 "multires_1d_xy", "multires_1d_renewal", "grid_var_bruteforce_iso", "grid_ls_multires_iso", "grid_ls_var_multires_1d",
                 "proc_mean_two_spheres_iso", "proc_mean_grid_sdf_iso", "proc_mean_knob_inner_1d", "aniso_mtx_iso_renewalplus", "aniso_mtx_multires_iso",
-                "fbm_sandstone_var_bruteforce_iso", "fbm_rust_ls_multires_iso"]
+                "fbm_sandstone_var_bruteforce_iso", "fbm_rust_ls_multires_iso",
+                # the kernel variants added late in round 2 (full-matrix kernels, Matern / Gabor, procedural means on the cached marches): profiles/r02_parity_rates_late_kernels.txt
+                "aniso_mtx_world_renewalplus", "aniso_mtx_1d_xy_mis", "aniso_rot_world_bruteforce", "aniso_rot_iso_multires", "aniso_rot_iso_const_none",
+                "aniso_rot_world_multires_renewal", "matern05_world", "matern15_world", "gabor_aniso_world", "proc_mean_knob_iso", "proc_mean_plane_world"]
 
 
 def checker(medium_json):

@@ -182,6 +182,10 @@ PARITY_BOUNDS = {(n, sec): _FD for n in ("proc_mean_two_spheres_iso", "proc_mean
 # field is bit-identical at a given point (golden media); the hit POINT differs by an ulp between the implementations.
 _ROUGH = (3, 3, 1e-4, 5e-3, 1e-3, 1e-3)
 PARITY_BOUNDS.update({("fbm_rust_ls_multires_iso", sec): _ROUGH for sec in (False, True)})
+PARITY_BOUNDS.update({(n, sec): _FD for n in ("proc_mean_knob_iso", "proc_mean_plane_world") for sec in (False, True)})
+# Matern nu = 1/2 (a kernel with a cusp at the impulse) and Gabor: ONE primary ray of 8192 whose gradient is nearly zero sits at 2.2e-3 / 4.4e-3 of the rms
+# gradient; the 99.9 % quantile is 2.5e-5 / 5e-6 (profiles/r02_parity_rates_late_kernels.txt)
+PARITY_BOUNDS.update({(n, sec): (3, 3, 1e-4, 6e-3, 1e-3, TOL) for n in ("matern05_world", "gabor_aniso_world") for sec in (False, True)})
 
 
 @pytest.mark.parametrize("secondary", [False, True])

@@ -1,7 +1,7 @@
 """Developer tool: the large-sample query parity of tests/test_gpu_parity.py::test_march_kernels_vs_reference_8k_rays as a table of
 RATES (run on the GPU box; copy the output to profiles/).  Checker = oracle/_ref (the compiled, unmodified reference).
 
-  python tools/parity_rates.py [rays, default 8192] > gpurun_out/parity_rates.txt
+  python tools/parity_rates.py [rays, default 8192] [medium names, default tests/support.py PARITY_MEDIA] > gpurun_out/parity_rates.txt
 """
 import json
 import os
@@ -17,7 +17,7 @@ print("# decision = ok/exited differ or hit > 1 march step away; step_moved = sa
 print("# matched = the rest: relative errors of t (floor 1e-3), gradient (floor: rms), the 7 conditioning coefficients (floor: rms of each)")
 print("%-36s %-9s %8s %5s %5s %9s %9s %9s %9s %9s %9s %4s" % ("medium", "wavefront", "hit_frac", "dec", "moved", "t_max", "t_p999", "grad_max", "grad_p999", "ctx_max", "ctx_p999", "T!="))
 rows = []
-for name in S.PARITY_MEDIA:
+for name in (sys.argv[2:] or S.PARITY_MEDIA):
     for secondary in (False, True):
         r = S.query_parity_case(name, secondary, n=n)
         rows.append(r)
